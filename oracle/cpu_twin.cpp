@@ -1,0 +1,96 @@
+// ORACLE / CPU BASELINE — test and benchmark infrastructure only, never on the product path.
+//
+// "C++ CPU twin" of SURVEY.md §8d / BASELINE.md §3: the same interior-point + Riccati algorithm and the same
+// model functions as the CUDA solver (it includes the product headers), compiled for the host in float64,
+// one problem per thread, OpenMP over the batch.  It stands in for the reference's CPU path — the
+// FORCESPRO-generated C solver called at planner/mpcPlanner.py:262, which is proprietary and absent — as the
+// timed CPU baseline (`cpu_baseline.kind = "port"`), and gives a CUDA-independent execution of the algorithm
+// for debugging.  The independent correctness oracle is oracle/solve.py (scipy), not this file.
+//
+// build: g++ -O3 -march=native -fopenmp -std=c++17 -shared -fPIC -I <solver_dir> -I robot_mpcs_b200/csrc
+#include <omp.h>
+#include <cstring>
+#include "model_traits.h"
+#include "rmpc_ipm.cuh"
+
+using M = ModelTraits;
+
+template <class T, class TF>
+static void run(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
+                int* iters, double* resid, const rmpc::Options& opt) {
+#pragma omp parallel
+  {
+    auto* w = new rmpc::Work<M, T>();
+    T* p = new T[M::N * M::NPAR];
+#pragma omp for schedule(dynamic, 8)
+    for (int b = 0; b < B; ++b) {
+      for (int k = 0; k < M::N; ++k)
+        for (int i = 0; i < M::NVAR; ++i) w->z[k][i] = T(x0[(size_t(b) * M::N + k) * M::NVAR + i]);
+      for (int i = 0; i < M::N * M::NPAR; ++i) p[i] = T(params[size_t(b) * M::N * M::NPAR + i]);
+      T xi[M::NX];
+      for (int i = 0; i < M::NX; ++i) xi[i] = T(xinit[size_t(b) * M::NX + i]);
+      rmpc::ParamView<T> pv{p, M::NPAR, 1};
+      rmpc::Info info;
+      rmpc::solve_one<M, T, TF>(*w, xi, pv, opt, info);
+      for (int k = 0; k < M::N; ++k)
+        for (int i = 0; i < M::NVAR; ++i) z_out[(size_t(b) * M::N + k) * M::NVAR + i] = double(w->z[k][i]);
+      exitflag[b] = info.exitflag;
+      iters[b] = info.iters;
+      if (resid) {
+        double* r = resid + size_t(b) * 6;
+        r[0] = info.obj; r[1] = info.res_stat; r[2] = info.res_eq; r[3] = info.res_ineq; r[4] = info.res_comp; r[5] = info.mu;
+      }
+    }
+    delete w;
+    delete[] p;
+  }
+}
+
+extern "C" {
+const char* twin_name() { return M::NAME; }
+void twin_dims(int* d) { d[0] = M::N; d[1] = M::NX; d[2] = M::NU; d[3] = M::NVAR; d[4] = M::NPAR; d[5] = M::NH; }
+int twin_max_threads() { return omp_get_max_threads(); }
+
+// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg]; precision: 0 f64, 1 f64+f32 factor, 2 f32
+int twin_solve_batch(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
+                     int* iters, double* resid, const double* opts, int nthreads, int precision) {
+  rmpc::Options o = rmpc::default_options();
+  if (opts) {
+    o.max_iter = int(opts[0]); o.hessian = int(opts[1]); o.tol_stat = opts[2]; o.tol_eq = opts[3]; o.tol_ineq = opts[4];
+    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8];
+  }
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+  if (precision == 0) run<double, double>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
+  else if (precision == 1) run<double, float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
+  else run<float, float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
+  return 0;
+}
+
+// model-function probes for the derivative / FK parity tests
+void twin_stage_values(const double* z, const double* p, double* f, double* h) {
+  rmpc::StageVal<M, double> sv;
+  rmpc::stage_values<M, double>(z, p, sv);
+  *f = sv.f;
+  for (int i = 0; i < M::NH; ++i) h[i] = sv.h[i];
+}
+void twin_dynamics(const double* z, double* xn, double* AB) {
+  rmpc::dyn_derivatives<M, double, false>(z, xn, AB, nullptr, nullptr);
+}
+// exact: Hqq includes rho/kappa terms; returns cost grad g[NVAR], Hqq[NQ*NQ], Hd[NVAR], h[NH], Gg[NGEO*NQ]
+void twin_stage_derivatives(const double* z, const double* p, const double* rho, const double* kappa, int exact,
+                            double* f, double* g, double* Hqq, double* Hd, double* h, double* Gg) {
+  rmpc::StageDer<M, double> sd;
+  if (exact) rmpc::stage_derivatives<M, double, true>(z, p, rho, kappa, sd);
+  else rmpc::stage_derivatives<M, double, false>(z, p, rho, kappa, sd);
+  *f = sd.f;
+  for (int i = 0; i < M::NVAR; ++i) { g[i] = sd.g[i]; Hd[i] = sd.Hd[i]; }
+  for (int i = 0; i < M::NQ * M::NQ; ++i) Hqq[i] = sd.Hqq[i];
+  for (int i = 0; i < M::NH; ++i) h[i] = sd.h[i];
+  for (int r = 0; r < M::NGEO; ++r)
+    for (int i = 0; i < M::NQ; ++i) Gg[r * M::NQ + i] = sd.Gg[r][i];
+}
+void twin_dyn_curvature(const double* z, const double* nu, double* Q) {
+  double xn[M::NX], AB[M::NX * M::NVAR];
+  rmpc::dyn_derivatives<M, double, true>(z, xn, AB, nu, Q);
+}
+}

@@ -1,0 +1,562 @@
+// rmpc_model.cuh — per-stage model functions of the robotmpcs NLP as fused device functions with analytic
+// Jacobians and (Gauss-Newton or exact) Hessians.  Everything is templated on a generated `M` traits struct
+// (robot_mpcs_b200/models/codegen.py) so the compiler sees every dimension, every kinematic constant and
+// every parameter index as an immediate.
+//
+// What is restated here (reference paths relative to /root/reference):
+//   forward kinematics      forwardkinematics.GenericURDFFk, call sites models/mpcBase.py:46-51,89-94
+//   RadialConstraints       models/mpcBase.py:82-101, inequalities/RadialConstraints.py
+//   LinearConstraints       inequalities/LinearConstraints.py:25-40, utils/utils.py:48-52
+//   SelfCollision...        inequalities/SelfCollisionAvoidanceConstraints.py:18-27
+//   Joint/Input/VelLimit    inequalities/{JointLimit,InputLimit,VelLimit}Constraints.py
+//   GoalReaching            objectives/goal_reaching.py:19-34
+//   ConstraintAvoidance     objectives/constraint_avoidance.py:25-32
+//   objective               objectives/ObjectiveManager.py:28-46
+//   dynamics                models/mpcModel.py:65-69,118-120, models/diff_drive_mpc_model.py:24-41
+#pragma once
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define RMPC_HD __host__ __device__ __forceinline__
+#else
+#define RMPC_HD inline __attribute__((always_inline))
+#endif
+
+#if defined(__CUDA_ARCH__)
+#define RMPC_UNROLL _Pragma("unroll")
+#else
+#define RMPC_UNROLL
+#endif
+
+namespace rmpc {
+
+template <class T> RMPC_HD T tmax(T a, T b) { return a > b ? a : b; }
+template <class T> RMPC_HD T tmin(T a, T b) { return a < b ? a : b; }
+template <class T> RMPC_HD T tabs(T a) { return a < T(0) ? -a : a; }
+RMPC_HD float tsqrt(float a) { return sqrtf(a); }
+RMPC_HD double tsqrt(double a) { return sqrt(a); }
+RMPC_HD void tsincos(float a, float* s, float* c) { *s = sinf(a); *c = cosf(a); }
+RMPC_HD void tsincos(double a, double* s, double* c) { *s = sin(a); *c = cos(a); }
+RMPC_HD float tlog(float a) { return logf(a); }
+RMPC_HD double tlog(double a) { return log(a); }
+
+// ------------------------------------------------------------------------------------------------
+// Kinematics: world frames of the NJ tree joints that matter, positions of the NPT points of interest
+// and their position Jacobians w.r.t. q.
+// ------------------------------------------------------------------------------------------------
+template <class M, class T>
+struct Kin {
+  T R[M::NJ > 0 ? M::NJ : 1][9];   // world rotation of the child-link frame of joint j
+  T t[M::NJ > 0 ? M::NJ : 1][3];   // world origin of that frame
+  T a[M::NJ > 0 ? M::NJ : 1][3];   // world axis of joint j
+  T p[M::NPT > 0 ? M::NPT : 1][3];            // points of interest
+  T Jp[M::NPT > 0 ? M::NPT : 1][3][M::NQ];    // d p / d q
+};
+
+template <class M, class T>
+RMPC_HD void kin_frames(const T* q, Kin<M, T>& kn) {
+  RMPC_UNROLL
+  for (int j = 0; j < M::NJ; ++j) {
+    const int par = M::j_parent(j);
+    T Rp[9], tp[3];
+    if (par < 0) {
+      RMPC_UNROLL
+      for (int i = 0; i < 9; ++i) Rp[i] = T((i % 4) == 0 ? 1 : 0);
+      tp[0] = tp[1] = tp[2] = T(0);
+    } else {
+      RMPC_UNROLL
+      for (int i = 0; i < 9; ++i) Rp[i] = kn.R[par][i];
+      RMPC_UNROLL
+      for (int i = 0; i < 3; ++i) tp[i] = kn.t[par][i];
+    }
+    T Ro[9], to[3];
+    RMPC_UNROLL
+    for (int r = 0; r < 3; ++r) {
+      to[r] = tp[r];
+      RMPC_UNROLL
+      for (int c = 0; c < 3; ++c) {
+        if (M::j_T(j, c) != 0.0) to[r] += Rp[3 * r + c] * T(M::j_T(j, c));
+        T acc = T(0);
+        RMPC_UNROLL
+        for (int k = 0; k < 3; ++k)
+          if (M::j_R(j, 3 * k + c) != 0.0) acc += Rp[3 * r + k] * T(M::j_R(j, 3 * k + c));
+        Ro[3 * r + c] = acc;
+      }
+    }
+    T aw[3];
+    RMPC_UNROLL
+    for (int r = 0; r < 3; ++r) {
+      T acc = T(0);
+      RMPC_UNROLL
+      for (int k = 0; k < 3; ++k)
+        if (M::j_axis(j, k) != 0.0) acc += Ro[3 * r + k] * T(M::j_axis(j, k));
+      aw[r] = acc;
+      kn.a[j][r] = acc;
+    }
+    const int typ = M::j_type(j);
+    if (typ == 2) {  // prismatic
+      const T qj = q[M::j_q(j)];
+      RMPC_UNROLL
+      for (int r = 0; r < 3; ++r) to[r] += aw[r] * qj;
+    } else if (typ == 1) {  // revolute: Ro <- Ro * Rot(axis, q)  (Rodrigues, constant local axis)
+      T s, c;
+      tsincos(q[M::j_q(j)], &s, &c);
+      const T v = T(1) - c;
+      T Rj[9];
+      const double ax = M::j_axis(j, 0), ay = M::j_axis(j, 1), az = M::j_axis(j, 2);
+      Rj[0] = c + T(ax * ax) * v;      Rj[1] = T(ax * ay) * v - T(az) * s; Rj[2] = T(ax * az) * v + T(ay) * s;
+      Rj[3] = T(ay * ax) * v + T(az) * s; Rj[4] = c + T(ay * ay) * v;      Rj[5] = T(ay * az) * v - T(ax) * s;
+      Rj[6] = T(az * ax) * v - T(ay) * s; Rj[7] = T(az * ay) * v + T(ax) * s; Rj[8] = c + T(az * az) * v;
+      T Rn[9];
+      RMPC_UNROLL
+      for (int r = 0; r < 3; ++r)
+        RMPC_UNROLL
+        for (int cc = 0; cc < 3; ++cc)
+          Rn[3 * r + cc] = Ro[3 * r] * Rj[cc] + Ro[3 * r + 1] * Rj[3 + cc] + Ro[3 * r + 2] * Rj[6 + cc];
+      RMPC_UNROLL
+      for (int i = 0; i < 9; ++i) Ro[i] = Rn[i];
+    }
+    RMPC_UNROLL
+    for (int i = 0; i < 9; ++i) kn.R[j][i] = Ro[i];
+    RMPC_UNROLL
+    for (int i = 0; i < 3; ++i) kn.t[j][i] = to[i];
+  }
+}
+
+template <class T> RMPC_HD void cross3(const T* a, const T* b, T* o) {
+  o[0] = a[1] * b[2] - a[2] * b[1];
+  o[1] = a[2] * b[0] - a[0] * b[2];
+  o[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+template <class M, class T, bool JAC>
+RMPC_HD void kin_points(const T* q, Kin<M, T>& kn) {
+  kin_frames<M, T>(q, kn);
+  RMPC_UNROLL
+  for (int i = 0; i < M::NPT; ++i) {
+    const int jl = M::pt_joint(i);
+    RMPC_UNROLL
+    for (int c = 0; c < 3; ++c) kn.p[i][c] = (jl < 0) ? T(0) : kn.t[jl][c];
+    if (JAC) {
+      RMPC_UNROLL
+      for (int c = 0; c < 3; ++c)
+        RMPC_UNROLL
+        for (int k = 0; k < M::NQ; ++k) kn.Jp[i][c][k] = T(0);
+      RMPC_UNROLL
+      for (int j = 0; j < M::NJ; ++j) {
+        if (!((M::pt_mask(i) >> j) & 1u)) continue;
+        const int typ = M::j_type(j);
+        if (typ == 0) continue;
+        const int qi = M::j_q(j);
+        if (typ == 2) {
+          RMPC_UNROLL
+          for (int c = 0; c < 3; ++c) kn.Jp[i][c][qi] = kn.a[j][c];
+        } else {
+          T d[3], cr[3];
+          RMPC_UNROLL
+          for (int c = 0; c < 3; ++c) d[c] = kn.p[i][c] - kn.t[j][c];
+          cross3(kn.a[j], d, cr);
+          RMPC_UNROLL
+          for (int c = 0; c < 3; ++c) kn.Jp[i][c][qi] = cr[c];
+        }
+      }
+    }
+  }
+}
+
+// Sum_c w[c] * d^2 p_c / dq dq  added into Hqq (row-major NQ x NQ, both triangles).
+template <class M, class T>
+RMPC_HD void kin_point_curvature(const Kin<M, T>& kn, int i, const T* w, T* Hqq) {
+  RMPC_UNROLL
+  for (int k = 0; k < M::NJ; ++k) {
+    if (!((M::pt_mask(i) >> k) & 1u)) continue;
+    const int tk = M::j_type(k);
+    if (tk == 0) continue;
+    T inner[3];
+    if (tk == 1) {
+      T d[3];
+      RMPC_UNROLL
+      for (int c = 0; c < 3; ++c) d[c] = kn.p[i][c] - kn.t[k][c];
+      cross3(kn.a[k], d, inner);
+    } else {
+      RMPC_UNROLL
+      for (int c = 0; c < 3; ++c) inner[c] = kn.a[k][c];
+    }
+    RMPC_UNROLL
+    for (int j = 0; j <= k; ++j) {  // j is an ancestor of (or equal to) k
+      if (!((M::pt_mask(i) >> j) & 1u)) continue;
+      if (M::j_type(j) != 1) continue;  // only an upstream revolute joint bends the downstream column
+      T v[3];
+      cross3(kn.a[j], inner, v);
+      const T val = w[0] * v[0] + w[1] * v[1] + w[2] * v[2];
+      const int qj = M::j_q(j), qk = M::j_q(k);
+      Hqq[qj * M::NQ + qk] += val;
+      if (qj != qk) Hqq[qk * M::NQ + qj] += val;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Stage functions
+// ------------------------------------------------------------------------------------------------
+constexpr int GEO_SPHERE = 0, GEO_PLANE = 1, GEO_PAIR = 2;
+
+template <class M, class T>
+struct StageVal {  // values only (line search)
+  T f;
+  T h[M::NH];
+  bool pole;  // a ConstraintAvoidance row is on the wrong side of its pole (h <= 0)
+};
+
+template <class M, class T>
+struct StageDer {
+  T f;
+  T g[M::NVAR];                      // cost gradient
+  T Hqq[M::NQ * M::NQ];              // d2/dq2 of (cost + barrier rank-1 + optional curvature), full symmetric
+  T Hd[M::NVAR];                     // diagonal part of the cost Hessian for every variable
+  T h[M::NH];
+  T Gg[M::NGEO > 0 ? M::NGEO : 1][M::NQ];  // gradients of the geometric rows w.r.t. q
+  bool pole;
+};
+
+// geometric row r: value + unit direction(s) in point space
+template <class M, class T>
+RMPC_HD T geo_value(const Kin<M, T>& kn, const T* p, int r, T* nvec, T* dist_out) {
+  const int typ = M::geo_type(r), A = M::geo_a(r);
+  const T rb = p[M::geo_rb(r)];
+  if (typ == GEO_SPHERE) {
+    const int o = M::geo_p(r);
+    T d[3] = {kn.p[A][0] - p[o], kn.p[A][1] - p[o + 1], kn.p[A][2] - p[o + 2]};
+    const T dist = tsqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    const T inv = T(1) / tmax(dist, T(1e-12));
+    nvec[0] = d[0] * inv; nvec[1] = d[1] * inv; nvec[2] = d[2] * inv;
+    *dist_out = dist;
+    return dist - p[o + 3] - rb;
+  } else if (typ == GEO_PLANE) {
+    const int o = M::geo_p(r);
+    const T v = p[o] * kn.p[A][0] + p[o + 1] * kn.p[A][1] + p[o + 2] * kn.p[A][2] + p[o + 3];
+    const T nrm = tsqrt(p[o] * p[o] + p[o + 1] * p[o + 1] + p[o + 2] * p[o + 2]);
+    const T sg = (v < T(0) ? T(-1) : T(1)) / nrm;
+    nvec[0] = sg * p[o]; nvec[1] = sg * p[o + 1]; nvec[2] = sg * p[o + 2];
+    *dist_out = T(0);
+    return tabs(v) / nrm - rb;
+  } else {
+    const int Bp = M::geo_b(r);
+    T d[3] = {kn.p[A][0] - kn.p[Bp][0], kn.p[A][1] - kn.p[Bp][1], kn.p[A][2] - kn.p[Bp][2]};
+    const T dist = tsqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    const T inv = T(1) / tmax(dist, T(1e-12));
+    nvec[0] = d[0] * inv; nvec[1] = d[1] * inv; nvec[2] = d[2] * inv;
+    *dist_out = dist;
+    return dist - T(2) * rb;
+  }
+}
+
+template <class M, class T>
+RMPC_HD void stage_values(const T* z, const T* p, StageVal<M, T>& out) {
+  Kin<M, T> kn;
+  kin_points<M, T, false>(z, kn);
+  RMPC_UNROLL
+  for (int r = 0; r < M::NGEO; ++r) {
+    T nv[3], dist;
+    out.h[M::geo_row(r)] = geo_value<M, T>(kn, p, r, nv, &dist);
+  }
+  RMPC_UNROLL
+  for (int r = 0; r < M::NLIM; ++r) {
+    const T zv = z[M::lim_var(r)], pv = p[M::lim_p(r)];
+    out.h[M::lim_row(r)] = M::lim_sign(r) > 0 ? zv - pv : pv - zv;
+  }
+  T f = T(0);
+  if (M::GOAL_PT >= 0) {
+    RMPC_UNROLL
+    for (int c = 0; c < 3; ++c) {
+      const T e = kn.p[M::GOAL_PT >= 0 ? M::GOAL_PT : 0][c] - p[M::P_GOAL + c];
+      f += p[M::P_WGOAL + c] * e * e;
+    }
+  }
+  bool pole = false;
+  RMPC_UNROLL
+  for (int i = 0; i < M::NCA; ++i) {
+    const T w = p[M::ca_w(i)];
+    const T hv = out.h[M::ca_row(i)];
+    if (w != T(0)) {
+      if (hv <= T(0)) pole = true;
+      f += T(M::N) * w / hv;
+    }
+  }
+  RMPC_UNROLL
+  for (int j = 0; j < M::NU; ++j) f += p[M::P_WU + j] * z[M::NX + j] * z[M::NX + j];
+  out.f = f;
+  out.pole = pole;
+}
+
+// rho[r]   : coefficient of g_r g_r' for geometric row r (barrier lambda/s), CA rank-1 is added inside
+// kappa[r] : coefficient of the row's own Hessian (-lambda_r); CA adds -N w / h^2.  Used only if EXACT.
+template <class M, class T, bool EXACT>
+RMPC_HD void stage_derivatives(const T* z, const T* p, const T* rho, const T* kappa, StageDer<M, T>& out) {
+  Kin<M, T> kn;
+  kin_points<M, T, true>(z, kn);
+  RMPC_UNROLL
+  for (int i = 0; i < M::NQ * M::NQ; ++i) out.Hqq[i] = T(0);
+  RMPC_UNROLL
+  for (int i = 0; i < M::NVAR; ++i) { out.g[i] = T(0); out.Hd[i] = T(0); }
+  T wv[M::NPT > 0 ? M::NPT : 1][3];   // per-point weight of the FK second derivative (EXACT)
+  T cJJ[M::NPT > 0 ? M::NPT : 1];     // per-point coefficient of Jp'Jp (EXACT)
+  RMPC_UNROLL
+  for (int i = 0; i < M::NPT; ++i) { wv[i][0] = wv[i][1] = wv[i][2] = T(0); cJJ[i] = T(0); }
+  T nvec[M::NGEO > 0 ? M::NGEO : 1][3], dist[M::NGEO > 0 ? M::NGEO : 1];
+  T r1[M::NGEO > 0 ? M::NGEO : 1], kap[M::NGEO > 0 ? M::NGEO : 1];
+  // geometric rows: value, gradient
+  RMPC_UNROLL
+  for (int r = 0; r < M::NGEO; ++r) {
+    out.h[M::geo_row(r)] = geo_value<M, T>(kn, p, r, nvec[r], &dist[r]);
+    const int A = M::geo_a(r);
+    RMPC_UNROLL
+    for (int k = 0; k < M::NQ; ++k) {
+      T gk = nvec[r][0] * kn.Jp[A][0][k] + nvec[r][1] * kn.Jp[A][1][k] + nvec[r][2] * kn.Jp[A][2][k];
+      if (M::geo_type(r) == GEO_PAIR) {
+        const int Bp = M::geo_b(r);
+        gk -= nvec[r][0] * kn.Jp[Bp][0][k] + nvec[r][1] * kn.Jp[Bp][1][k] + nvec[r][2] * kn.Jp[Bp][2][k];
+      }
+      out.Gg[r][k] = gk;
+    }
+    r1[r] = rho[r];
+    kap[r] = EXACT ? kappa[r] : T(0);
+  }
+  RMPC_UNROLL
+  for (int r = 0; r < M::NLIM; ++r) {
+    const T zv = z[M::lim_var(r)], pv = p[M::lim_p(r)];
+    out.h[M::lim_row(r)] = M::lim_sign(r) > 0 ? zv - pv : pv - zv;
+  }
+  T f = T(0);
+  // GoalReaching
+  if (M::GOAL_PT >= 0) {
+    constexpr int E = M::GOAL_PT >= 0 ? M::GOAL_PT : 0;
+    T we[3];
+    RMPC_UNROLL
+    for (int c = 0; c < 3; ++c) {
+      const T e = kn.p[E][c] - p[M::P_GOAL + c];
+      const T w = p[M::P_WGOAL + c];
+      f += w * e * e;
+      we[c] = T(2) * w * e;
+      if (EXACT) wv[E][c] += we[c];
+    }
+    RMPC_UNROLL
+    for (int k = 0; k < M::NQ; ++k) {
+      out.g[k] += we[0] * kn.Jp[E][0][k] + we[1] * kn.Jp[E][1][k] + we[2] * kn.Jp[E][2][k];
+      RMPC_UNROLL
+      for (int l = 0; l <= k; ++l) {
+        T v = T(0);
+        RMPC_UNROLL
+        for (int c = 0; c < 3; ++c) v += T(2) * p[M::P_WGOAL + c] * kn.Jp[E][c][k] * kn.Jp[E][c][l];
+        out.Hqq[k * M::NQ + l] += v;
+        if (l != k) out.Hqq[l * M::NQ + k] += v;
+      }
+    }
+  }
+  // ConstraintAvoidance: N * w / h on the first row of each module
+  bool pole = false;
+  RMPC_UNROLL
+  for (int i = 0; i < M::NCA; ++i) {
+    const T w = p[M::ca_w(i)];
+    if (w == T(0)) continue;
+    const int row = M::ca_row(i);
+    const T hv = out.h[row];
+    if (hv <= T(0)) pole = true;
+    const T ih = T(1) / hv;
+    const T c0 = T(M::N) * w * ih;   // value
+    const T c1 = -c0 * ih;           // d/dh
+    const T c2 = T(2) * c0 * ih * ih;  // d2/dh2
+    f += c0;
+    if (M::ca_geo(i) >= 0) {
+      const int r = M::ca_geo(i) >= 0 ? M::ca_geo(i) : 0;
+      RMPC_UNROLL
+      for (int k = 0; k < M::NQ; ++k) out.g[k] += c1 * out.Gg[r][k];
+      r1[r] += c2;
+      if (EXACT) kap[r] += c1;
+    } else {
+      const int l = M::ca_lim(i) >= 0 ? M::ca_lim(i) : 0;
+      out.g[M::lim_var(l)] += c1 * T(M::lim_sign(l));
+      out.Hd[M::lim_var(l)] += c2;
+    }
+  }
+  // rank-1 and curvature of the geometric rows
+  RMPC_UNROLL
+  for (int r = 0; r < M::NGEO; ++r) {
+    T c = r1[r];
+    if (EXACT && M::geo_type(r) != GEO_PLANE) {
+      const T kd = kap[r] / tmax(dist[r], T(1e-12));
+      c -= kd;  // kappa (I - n n')/dist  ->  -kappa/dist g g'  + kappa/dist J'J
+      if (M::geo_type(r) == GEO_SPHERE) {
+        cJJ[M::geo_a(r)] += kd;
+      } else {
+        const int A = M::geo_a(r), Bp = M::geo_b(r);
+        RMPC_UNROLL
+        for (int k = 0; k < M::NQ; ++k)
+          RMPC_UNROLL
+          for (int l = 0; l <= k; ++l) {
+            T v = T(0);
+            RMPC_UNROLL
+            for (int cc = 0; cc < 3; ++cc) v += (kn.Jp[A][cc][k] - kn.Jp[Bp][cc][k]) * (kn.Jp[A][cc][l] - kn.Jp[Bp][cc][l]);
+            v *= kd;
+            out.Hqq[k * M::NQ + l] += v;
+            if (l != k) out.Hqq[l * M::NQ + k] += v;
+          }
+      }
+    }
+    if (EXACT) {
+      RMPC_UNROLL
+      for (int cc = 0; cc < 3; ++cc) {
+        wv[M::geo_a(r)][cc] += kap[r] * nvec[r][cc];
+        if (M::geo_type(r) == GEO_PAIR) wv[M::geo_b(r) >= 0 ? M::geo_b(r) : 0][cc] -= kap[r] * nvec[r][cc];
+      }
+    }
+    RMPC_UNROLL
+    for (int k = 0; k < M::NQ; ++k)
+      RMPC_UNROLL
+      for (int l = 0; l <= k; ++l) {
+        const T v = c * out.Gg[r][k] * out.Gg[r][l];
+        out.Hqq[k * M::NQ + l] += v;
+        if (l != k) out.Hqq[l * M::NQ + k] += v;
+      }
+  }
+  if (EXACT) {
+    RMPC_UNROLL
+    for (int i = 0; i < M::NPT; ++i) {
+      if (M::pt_mask(i) == 0u) continue;
+      RMPC_UNROLL
+      for (int k = 0; k < M::NQ; ++k)
+        RMPC_UNROLL
+        for (int l = 0; l <= k; ++l) {
+          T v = T(0);
+          RMPC_UNROLL
+          for (int cc = 0; cc < 3; ++cc) v += kn.Jp[i][cc][k] * kn.Jp[i][cc][l];
+          v *= cJJ[i];
+          out.Hqq[k * M::NQ + l] += v;
+          if (l != k) out.Hqq[l * M::NQ + k] += v;
+        }
+      kin_point_curvature<M, T>(kn, i, wv[i], out.Hqq);
+    }
+  }
+  // u' diag(wu) u
+  RMPC_UNROLL
+  for (int j = 0; j < M::NU; ++j) {
+    const T w = p[M::P_WU + j], u = z[M::NX + j];
+    f += w * u * u;
+    out.g[M::NX + j] += T(2) * w * u;
+    out.Hd[M::NX + j] += T(2) * w;
+  }
+  out.f = f;
+  out.pole = pole;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Discrete dynamics x+ = Phi(x,u): ERK2 (explicit midpoint), Ts = dt, 5 nodes.
+//   holonomic double integrator: exact closed form (any 2-stage order-2 ERK gives it)
+//   diffdrive: closed form of the 5 midpoint substeps (angles/speeds are polynomial in the substep index)
+// ------------------------------------------------------------------------------------------------
+template <class M, class T>
+RMPC_HD void dyn_value(const T* z, T* xn) {
+  const T dt = T(M::DT);
+  if (M::BASE == 0) {
+    RMPC_UNROLL
+    for (int i = 0; i < M::NQ; ++i) {
+      xn[i] = z[i] + dt * z[M::NQ + i] + T(0.5) * dt * dt * z[M::NX + i];
+      xn[M::NQ + i] = z[M::NQ + i] + dt * z[M::NX + i];
+    }
+  } else {
+    const T h = dt / T(5);
+    const T th = z[2], v = z[6], om = z[7], u0 = z[8], u1 = z[9];
+    T dx = T(0), dy = T(0);
+    RMPC_UNROLL
+    for (int j = 0; j < 5; ++j) {
+      const T a = (T(j) + T(0.5)) * h, b = T(0.5) * T(j) * (T(j) + T(1)) * h * h;
+      T s, c;
+      tsincos(th + a * om + b * u1, &s, &c);
+      const T w = v + a * u0;
+      dx += h * c * w;
+      dy += h * s * w;
+    }
+    xn[0] = z[0] + dx; xn[1] = z[1] + dy; xn[2] = th + dt * om + T(0.5) * dt * dt * u1;
+    xn[3] = z[3]; xn[4] = z[4]; xn[5] = z[5];
+    xn[6] = v + dt * u0; xn[7] = om + dt * u1;
+  }
+}
+
+// AB is the NX x NVAR Jacobian [A B] (row-major).  If EXACT, nu (NX, multiplier of x+ = Phi) weights the
+// second derivative, added into Q (NVAR x NVAR row-major, both triangles).
+template <class M, class T, bool EXACT>
+RMPC_HD void dyn_derivatives(const T* z, T* xn, T* AB, const T* nu, T* Q) {
+  const T dt = T(M::DT);
+  RMPC_UNROLL
+  for (int i = 0; i < M::NX * M::NVAR; ++i) AB[i] = T(0);
+  if (M::BASE == 0) {
+    RMPC_UNROLL
+    for (int i = 0; i < M::NQ; ++i) {
+      xn[i] = z[i] + dt * z[M::NQ + i] + T(0.5) * dt * dt * z[M::NX + i];
+      xn[M::NQ + i] = z[M::NQ + i] + dt * z[M::NX + i];
+      AB[i * M::NVAR + i] = T(1);
+      AB[i * M::NVAR + M::NQ + i] = dt;
+      AB[i * M::NVAR + M::NX + i] = T(0.5) * dt * dt;
+      AB[(M::NQ + i) * M::NVAR + M::NQ + i] = T(1);
+      AB[(M::NQ + i) * M::NVAR + M::NX + i] = dt;
+    }
+  } else {
+    const T h = dt / T(5);
+    const T th = z[2], v = z[6], om = z[7], u0 = z[8], u1 = z[9];
+    T dx = T(0), dy = T(0);
+    // first derivatives of (dx,dy) w.r.t. [th, om, u1 | v, u0]
+    T gx[5] = {0, 0, 0, 0, 0}, gy[5] = {0, 0, 0, 0, 0};
+    T Hc[5][5];
+    if (EXACT) {
+      RMPC_UNROLL
+      for (int i = 0; i < 5; ++i)
+        RMPC_UNROLL
+        for (int j = 0; j < 5; ++j) Hc[i][j] = T(0);
+    }
+    RMPC_UNROLL
+    for (int j = 0; j < 5; ++j) {
+      const T a = (T(j) + T(0.5)) * h, b = T(0.5) * T(j) * (T(j) + T(1)) * h * h;
+      T s, c;
+      tsincos(th + a * om + b * u1, &s, &c);
+      const T w = v + a * u0;
+      dx += h * c * w;
+      dy += h * s * w;
+      const T gp[3] = {T(1), a, b};  // d phi / d(th,om,u1)
+      const T gw[2] = {T(1), a};     // d w / d(v,u0)
+      RMPC_UNROLL
+      for (int i = 0; i < 3; ++i) { gx[i] += -h * s * w * gp[i]; gy[i] += h * c * w * gp[i]; }
+      RMPC_UNROLL
+      for (int i = 0; i < 2; ++i) { gx[3 + i] += h * c * gw[i]; gy[3 + i] += h * s * gw[i]; }
+      if (EXACT) {
+        const T cpp = h * w * (-nu[0] * c - nu[1] * s);  // d2/dphi2
+        const T cpw = h * (-nu[0] * s + nu[1] * c);      // d2/dphi dw
+        RMPC_UNROLL
+        for (int i = 0; i < 3; ++i) {
+          RMPC_UNROLL
+          for (int l = 0; l < 3; ++l) Hc[i][l] += cpp * gp[i] * gp[l];
+          RMPC_UNROLL
+          for (int l = 0; l < 2; ++l) { Hc[i][3 + l] += cpw * gp[i] * gw[l]; Hc[3 + l][i] += cpw * gp[i] * gw[l]; }
+        }
+      }
+    }
+    xn[0] = z[0] + dx; xn[1] = z[1] + dy; xn[2] = th + dt * om + T(0.5) * dt * dt * u1;
+    xn[3] = z[3]; xn[4] = z[4]; xn[5] = z[5];
+    xn[6] = v + dt * u0; xn[7] = om + dt * u1;
+    const int vi[5] = {2, 7, 9, 6, 8};
+    AB[0 * M::NVAR + 0] = T(1); AB[1 * M::NVAR + 1] = T(1);
+    RMPC_UNROLL
+    for (int i = 0; i < 5; ++i) { AB[0 * M::NVAR + vi[i]] += gx[i]; AB[1 * M::NVAR + vi[i]] += gy[i]; }
+    AB[2 * M::NVAR + 2] = T(1); AB[2 * M::NVAR + 7] = dt; AB[2 * M::NVAR + 9] = T(0.5) * dt * dt;
+    AB[3 * M::NVAR + 3] = T(1); AB[4 * M::NVAR + 4] = T(1); AB[5 * M::NVAR + 5] = T(1);
+    AB[6 * M::NVAR + 6] = T(1); AB[6 * M::NVAR + 8] = dt;
+    AB[7 * M::NVAR + 7] = T(1); AB[7 * M::NVAR + 9] = dt;
+    if (EXACT) {
+      RMPC_UNROLL
+      for (int i = 0; i < 5; ++i)
+        RMPC_UNROLL
+        for (int l = 0; l < 5; ++l) Q[vi[i] * M::NVAR + vi[l]] += Hc[i][l];
+    }
+  }
+}
+
+}  // namespace rmpc
