@@ -1,0 +1,94 @@
+/* rmpc.h — C ABI of one generated batched-MPC solver library (lib<solverName>.so).
+ *
+ * Every solver directory written by MpcModel.generateSolver() holds one shared library that exports exactly
+ * these symbols, specialised for that model/horizon.  It is the drop-in for the FORCESPRO-generated
+ * solver the reference loads with `forcespro.nlp.Solver.from_directory(dir)` and calls with
+ * `solver.solve(problem)`:
+ *     /root/reference/robotmpcs/planner/mpcPlanner.py:73   (load)
+ *     /root/reference/robotmpcs/planner/mpcPlanner.py:246-250,262  (problem = {xinit, x0, all_parameters}; solve)
+ * with one change of shape: a call solves B independent problems.  Array layouts are the reference's own,
+ * with a leading batch dimension:
+ *     xinit  [B][nx]            problem["xinit"]            float64
+ *     x0     [B][N][nvar]       problem["x0"]               float64   (initial guess, stage-major)
+ *     params [B][N][npar]       problem["all_parameters"]   float64   (stage-major, paramMap.yaml indices)
+ *     z_out  [B][N][nvar]       output["x01".."xNN"]        float64
+ *     action [B][nu]            what mpcPlanner.py:275-281 slices out of the output
+ * Plain pointers and sizes only; no torch types.  All functions return 0 on success, negative on API error
+ * (message via rmpc_last_error()).  Per-problem solver status is reported only through info.exitflag[]
+ * with the FORCESPRO sign convention the reference tests (mpcPlanner.py:263): 1 optimal, 0 iteration limit,
+ * <0 failure (-5 factorisation, -6 NaN/Inf, -7 line search).
+ */
+#ifndef RMPC_H
+#define RMPC_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rmpc_solver rmpc_solver;
+
+typedef struct {
+  int N, nx, nu, nvar, npar, nh;
+  double dt;
+} rmpc_dims;
+
+typedef struct {
+  int max_iter;     /* iteration cap, default 200 (FORCESPRO default) */
+  int hessian;      /* 0 Gauss-Newton, 1 exact Lagrangian Hessian with Gauss-Newton fallback */
+  int precision;    /* 0: float64 throughout; 1: float64 iterates/residuals + float32 Riccati while mu is large */
+  int control_mode; /* 0 "acc": action = u of stage 1; 1 "vel": action = z_2[nvar-2nu : nvar-nu] (mpcPlanner.py:275-278) */
+  double tol_stat, tol_eq, tol_ineq, tol_comp;
+  double mu0, mu_min, reg;
+} rmpc_options;
+
+/* Per-problem diagnostics, structure of arrays of length B.  Device pointers for rmpc_solve_batch, host
+ * pointers for rmpc_solve_batch_host.  Any member may be NULL. */
+typedef struct {
+  int* exitflag;
+  int* iters;
+  double* obj;
+  double* res_stat;
+  double* res_eq;
+  double* res_ineq;
+  double* res_comp;
+} rmpc_info;
+
+const char* rmpc_model_name(void);
+int rmpc_get_dims(rmpc_dims* out);
+void rmpc_default_options(rmpc_options* out);
+const char* rmpc_last_error(void);
+
+/* Allocates the device workspace for up to max_batch problems on `device`. */
+rmpc_solver* rmpc_create(int device, int max_batch);
+void rmpc_destroy(rmpc_solver* s);
+int rmpc_set_options(rmpc_solver* s, const rmpc_options* opt);
+int rmpc_get_options(const rmpc_solver* s, rmpc_options* out);
+
+/* Solve B problems.  All array arguments are DEVICE pointers owned by the caller; the call is asynchronous
+ * on `stream` (a cudaStream_t passed as void*, NULL = default stream).  z_out / action_out / info may be NULL.
+ * Launches: 1 pack kernel, 1 solve kernel, 1 unpack kernel. */
+int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                     double* z_out, double* action_out, const rmpc_info* info, void* stream);
+
+/* Same with HOST pointers: copies inputs to the device, solves, copies results back, synchronises. */
+int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                          double* z_out, double* action_out, const rmpc_info* info);
+
+/* Warm start for `initialization: previous_plan` (mpcPlanner.py:215-226 shiftHorizon): x0[b][k] = z[b][k+1] for
+ * k < N-1, x0[b][N-1] = z[b][N-1].  Device pointers, [B][N][nvar] each; in-place (x0 == z) is allowed. */
+int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void* stream);
+
+/* Batched parameter scatter (the set* loops of mpcPlanner.py:120-210): for every problem b and every stage k,
+ * params[b][k][idx[j]] = values[b][j] (stage_varying == 0, values is [B][n_idx]) or values[b][k][j]
+ * (stage_varying == 1, values is [B][N][n_idx]).  idx is a HOST array of paramMap indices; the rest are device
+ * pointers. */
+int rmpc_set_params(rmpc_solver* s, int B, double* params, const int* idx, int n_idx, const double* values,
+                    int stage_varying, void* stream);
+
+/* Number of CUDA kernels this library has launched since it was loaded (bench.py reports it). */
+long rmpc_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

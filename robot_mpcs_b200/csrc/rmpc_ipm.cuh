@@ -13,6 +13,10 @@
 // part).  (T,TF) = (double,double) is the reference-grade path, (double,float) the mixed path.
 #pragma once
 #include "rmpc_model.cuh"
+#if defined(RMPC_TRACE)
+#include <stdio.h>
+#include <stdlib.h>
+#endif
 
 namespace rmpc {
 
@@ -49,7 +53,8 @@ struct Work {
   T lam[M::N][M::NH];
   T dz[M::N][M::NVAR];
   T K[M::N][M::NU * M::NX];
-  T kff[M::N][M::NU];
+  T kff0[M::N][M::NU];                               // feed-forward, mu-independent part
+  T kff1[M::N][M::NU];                               // feed-forward, coefficient of mu
   T gf[M::N][M::NVAR];                               // cost gradient
   T hh[M::N][M::NH];                                 // h(z)
   T Gg[M::N][M::NGEO > 0 ? M::NGEO : 1][M::NQ];      // geometric row gradients
@@ -97,10 +102,11 @@ RMPC_HD void sub_Gt(const Work<M, T>& w, int k, const T* y, T* out) {
   for (int r = 0; r < M::NLIM; ++r) out[M::lim_var(r)] -= T(M::lim_sign(r)) * y[M::lim_row(r)];
 }
 
-// Cholesky of the NU x NU block, solves for K = -Fuu^{-1} Fux and kff = -Fuu^{-1} fu.  Returns false if
-// a pivot is not positive (Hessian not positive definite on the null space of the dynamics).
+// Cholesky of the NU x NU block, then K = -Fuu^{-1} Fux and the two feed-forward vectors
+// kff0 = -Fuu^{-1} fu0 (mu-independent part of the gradient), kff1 = -Fuu^{-1} fu1 (coefficient of mu).
+// Returns false if a pivot is not positive (Hessian not positive definite on the null space of the dynamics).
 template <class M, class TF>
-RMPC_HD bool factor_solve(TF* Fuu, const TF* Fux, const TF* fu, TF* K, TF* kff) {
+RMPC_HD bool factor_solve(TF* Fuu, const TF* Fux, const TF* fu0, const TF* fu1, TF* K, TF* kff0, TF* kff1) {
   constexpr int NU = M::NU, NX = M::NX;
   RMPC_UNROLL
   for (int j = 0; j < NU; ++j) {
@@ -109,7 +115,7 @@ RMPC_HD bool factor_solve(TF* Fuu, const TF* Fux, const TF* fu, TF* K, TF* kff) 
     for (int k = 0; k < j; ++k) d -= Fuu[j * NU + k] * Fuu[j * NU + k];
     if (!(d > TF(0))) return false;
     const TF l = tsqrt(d), il = TF(1) / l;
-    Fuu[j * NU + j] = l;
+    Fuu[j * NU + j] = il;  // store the reciprocal pivot
     RMPC_UNROLL
     for (int i = j + 1; i < NU; ++i) {
       TF v = Fuu[i * NU + j];
@@ -118,28 +124,28 @@ RMPC_HD bool factor_solve(TF* Fuu, const TF* Fux, const TF* fu, TF* K, TF* kff) 
       Fuu[i * NU + j] = v * il;
     }
   }
-  // columns of [Fux | fu]
   RMPC_UNROLL
-  for (int c = 0; c <= NX; ++c) {
+  for (int c = 0; c < NX + 2; ++c) {
     TF y[NU];
     RMPC_UNROLL
     for (int i = 0; i < NU; ++i) {
-      TF v = (c < NX) ? Fux[i * NX + (c < NX ? c : 0)] : fu[i];
+      TF v = (c < NX) ? Fux[i * NX + (c < NX ? c : 0)] : (c == NX ? fu0[i] : fu1[i]);
       RMPC_UNROLL
       for (int k = 0; k < i; ++k) v -= Fuu[i * NU + k] * y[k];
-      y[i] = v / Fuu[i * NU + i];
+      y[i] = v * Fuu[i * NU + i];
     }
     RMPC_UNROLL
     for (int i = NU - 1; i >= 0; --i) {
       TF v = y[i];
       RMPC_UNROLL
       for (int k = i + 1; k < NU; ++k) v -= Fuu[k * NU + i] * y[k];
-      y[i] = v / Fuu[i * NU + i];
+      y[i] = v * Fuu[i * NU + i];
     }
     RMPC_UNROLL
     for (int i = 0; i < NU; ++i) {
       if (c < NX) K[i * NX + (c < NX ? c : 0)] = -y[i];
-      else kff[i] = -y[i];
+      else if (c == NX) kff0[i] = -y[i];
+      else kff1[i] = -y[i];
     }
   }
   return true;
@@ -147,24 +153,29 @@ RMPC_HD bool factor_solve(TF* Fuu, const TF* Fux, const TF* fu, TF* K, TF* kff) 
 
 template <class M, class T>
 struct SweepOut {
-  T res_stat, res_eq, res_ineq, res_comp, res_comp_mu;
+  T res_stat, res_eq, res_ineq;
+  T comp_min, comp_max; // extrema of s*lambda
   T f, theta, logs;     // objective, l1 infeasibility, sum log s
   T mult_sum;           // |nu|_1 + |lam|_1
   bool ok, pole, finite;
 };
 
 // One backward sweep at the current iterate: model derivatives, adjoint multipliers + KKT residuals,
-// condensed stage QP, Riccati factorisation.  EXACT selects the Hessian.
+// condensed stage QP, Riccati factorisation.  EXACT selects the Hessian.  The barrier parameter enters the
+// Newton system only through the gradient  -mu G'(1/s); the vector recursion is therefore carried twice
+// (mu-independent part and coefficient of mu) so that mu is chosen *after* the sweep, from the residuals
+// the sweep itself measured.
 template <class M, class T, class TF, bool EXACT>
-RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, SweepOut<M, T>& o) {
+RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T reg, SweepOut<M, T>& o) {
   constexpr int NX = M::NX, NU = M::NU, NV = M::NVAR, NH = M::NH, N = M::N;
-  TF P[NX * NX], pvec[NX];
+  TF P[NX * NX], p0[NX], p1[NX];
   T nu[NX];
   RMPC_UNROLL
   for (int i = 0; i < NX * NX; ++i) P[i] = TF(0);
   RMPC_UNROLL
-  for (int i = 0; i < NX; ++i) { pvec[i] = TF(0); nu[i] = T(0); }
-  o.res_stat = o.res_eq = o.res_ineq = o.res_comp = o.res_comp_mu = T(0);
+  for (int i = 0; i < NX; ++i) { p0[i] = TF(0); p1[i] = TF(0); nu[i] = T(0); }
+  o.res_stat = o.res_eq = o.res_ineq = T(0);
+  o.comp_min = T(1e30); o.comp_max = T(0);
   o.f = o.theta = o.logs = o.mult_sum = T(0);
   o.ok = true; o.pole = false; o.finite = true;
 
@@ -175,10 +186,10 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
     RMPC_UNROLL
     for (int i = 0; i < NV; ++i) zk[i] = w.z[k][i];
     // --- barrier quantities
-    T sig[NH], y[NH], lamk[NH];
+    T sig[NH], y0[NH], y1[NH], lamk[NH];
     T rho[M::NGEO > 0 ? M::NGEO : 1], kappa[M::NGEO > 0 ? M::NGEO : 1];
     RMPC_UNROLL
-    for (int r = 0; r < NH; ++r) { lamk[r] = w.lam[k][r]; sig[r] = lamk[r] / w.s[k][r]; }
+    for (int r = 0; r < NH; ++r) { lamk[r] = w.lam[k][r]; y1[r] = T(1) / w.s[k][r]; sig[r] = lamk[r] * y1[r]; }
     RMPC_UNROLL
     for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lamk[M::geo_row(r)]; }
     StageDer<M, T> sd;
@@ -190,11 +201,11 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
       const T sr = w.s[k][r];
       const T rh = sd.h[r] - sr;
       w.hh[k][r] = sd.h[r];
-      y[r] = mu / sr - sig[r] * sd.h[r] + lamk[r];
+      y0[r] = lamk[r] - sig[r] * sd.h[r];     // y = y0 + mu * y1
       o.res_ineq = tmax(o.res_ineq, tabs(rh));
       o.theta += tabs(rh);
-      o.res_comp = tmax(o.res_comp, tabs(sr * lamk[r]));
-      o.res_comp_mu = tmax(o.res_comp_mu, tabs(sr * lamk[r] - mu));
+      o.comp_max = tmax(o.comp_max, sr * lamk[r]);
+      o.comp_min = tmin(o.comp_min, sr * lamk[r]);
       o.logs += tlog(sr);
       o.mult_sum += tabs(lamk[r]);
     }
@@ -205,7 +216,7 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
     RMPC_UNROLL
     for (int i = 0; i < NV; ++i) w.gf[k][i] = sd.g[i];
 
-    // --- stage Hessian Q (NV x NV) and QP gradient qt = grad f - G'y ; Lagrangian gradient gl = grad f - G'lam
+    // --- stage Hessian Q (NV x NV); QP gradient qt0 + mu*qt1 = grad f - G'(y0 + mu y1); Lagrangian gradient gl
     T Q[NV * NV];
     RMPC_UNROLL
     for (int i = 0; i < NV * NV; ++i) Q[i] = T(0);
@@ -219,13 +230,14 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
     for (int r = 0; r < M::NLIM; ++r) Q[M::lim_var(r) * NV + M::lim_var(r)] += sig[M::lim_row(r)];
     RMPC_UNROLL
     for (int j = 0; j < NU; ++j) Q[(NX + j) * NV + NX + j] += reg;
-    T qt[NV], gl[NV];
+    T qt0[NV], qt1[NV], gl[NV];
     RMPC_UNROLL
-    for (int i = 0; i < NV; ++i) { qt[i] = sd.g[i]; gl[i] = sd.g[i]; }
-    sub_Gt<M, T>(w, k, y, qt);
+    for (int i = 0; i < NV; ++i) { qt0[i] = sd.g[i]; gl[i] = sd.g[i]; qt1[i] = T(0); }
+    sub_Gt<M, T>(w, k, y0, qt0);
+    sub_Gt<M, T>(w, k, y1, qt1);
     sub_Gt<M, T>(w, k, lamk, gl);
 
-    TF Fxx[NX * NX], Fux[NU * NX], Fuu[NU * NU], fx[NX], fu[NU];
+    TF Fxx[NX * NX], Fux[NU * NX], Fuu[NU * NU], fx0[NX], fu0[NU], fx1[NX], fu1[NU];
     if (k < N - 1) {
       // --- dynamics to the next stage: defect d, Jacobian [A B], adjoint, curvature
       T xn[NX], AB[NX * NV];
@@ -250,7 +262,7 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
       TF Pd[NX];
       RMPC_UNROLL
       for (int i = 0; i < NX; ++i) {
-        TF a = pvec[i];
+        TF a = p0[i];
         RMPC_UNROLL
         for (int j = 0; j < NX; ++j) a += P[i * NX + j] * TF(d[j]);
         Pd[i] = a;
@@ -267,10 +279,11 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
         }
       RMPC_UNROLL
       for (int i = 0; i < NV; ++i) {
-        TF gacc = TF(qt[i]);
+        TF g0 = TF(qt0[i]), g1 = TF(qt1[i]);
         RMPC_UNROLL
-        for (int l = 0; l < NX; ++l) gacc += TF(AB[l * NV + i]) * Pd[l];
-        if (i < NX) fx[i < NX ? i : 0] = gacc; else fu[i >= NX ? i - NX : 0] = gacc;
+        for (int l = 0; l < NX; ++l) { g0 += TF(AB[l * NV + i]) * Pd[l]; g1 += TF(AB[l * NV + i]) * p1[l]; }
+        if (i < NX) { fx0[i < NX ? i : 0] = g0; fx1[i < NX ? i : 0] = g1; }
+        else { fu0[i >= NX ? i - NX : 0] = g0; fu1[i >= NX ? i - NX : 0] = g1; }
         RMPC_UNROLL
         for (int j = 0; j <= i; ++j) {
           TF a = TF(Q[i * NV + j]);
@@ -284,7 +297,8 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
     } else {
       RMPC_UNROLL
       for (int i = 0; i < NV; ++i) {
-        if (i < NX) fx[i < NX ? i : 0] = TF(qt[i]); else fu[i >= NX ? i - NX : 0] = TF(qt[i]);
+        if (i < NX) { fx0[i < NX ? i : 0] = TF(qt0[i]); fx1[i < NX ? i : 0] = TF(qt1[i]); }
+        else { fu0[i >= NX ? i - NX : 0] = TF(qt0[i]); fu1[i >= NX ? i - NX : 0] = TF(qt1[i]); }
         RMPC_UNROLL
         for (int j = 0; j <= i; ++j) {
           const TF a = TF(Q[i * NV + j]);
@@ -300,19 +314,19 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T mu, T reg, 
     RMPC_UNROLL
     for (int i = 0; i < NX; ++i) nu[i] = gl[i];
 
-    TF Kk[NU * NX], kf[NU];
-    if (!factor_solve<M, TF>(Fuu, Fux, fu, Kk, kf)) { o.ok = false; return; }
+    TF Kk[NU * NX], kf0[NU], kf1[NU];
+    if (!factor_solve<M, TF>(Fuu, Fux, fu0, fu1, Kk, kf0, kf1)) { o.ok = false; return; }
     RMPC_UNROLL
     for (int i = 0; i < NU * NX; ++i) w.K[k][i] = T(Kk[i]);
     RMPC_UNROLL
-    for (int i = 0; i < NU; ++i) w.kff[k][i] = T(kf[i]);
+    for (int i = 0; i < NU; ++i) { w.kff0[k][i] = T(kf0[i]); w.kff1[k][i] = T(kf1[i]); }
     // P_k = Fxx + Fux' K ,  p_k = fx + Fux' kff
     RMPC_UNROLL
     for (int i = 0; i < NX; ++i) {
-      TF a = fx[i];
+      TF a0 = fx0[i], a1 = fx1[i];
       RMPC_UNROLL
-      for (int l = 0; l < NU; ++l) a += Fux[l * NX + i] * kf[l];
-      pvec[i] = a;
+      for (int l = 0; l < NU; ++l) { a0 += Fux[l * NX + i] * kf0[l]; a1 += Fux[l * NX + i] * kf1[l]; }
+      p0[i] = a0; p1[i] = a1;
       RMPC_UNROLL
       for (int j = 0; j <= i; ++j) {
         TF v = Fxx[i * NX + j];
@@ -350,35 +364,34 @@ RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, co
   info.exitflag = 0;
   int it = 0;
   SweepOut<M, T> so;
+  T res_comp = T(0);
   for (; it <= opt.max_iter; ++it) {
-    // ---- barrier parameter from the current complementarity (LOQO rule), monotone non-increasing
-    if (it > 0) {
-      T gap = T(0), mn = T(1e30);
-      for (int k = 0; k < N; ++k)
-        RMPC_UNROLL
-        for (int r = 0; r < NH; ++r) { const T c = w.s[k][r] * w.lam[k][r]; gap += c; mn = tmin(mn, c); }
-      const T avg = gap / T(N * NH);
-      const T xi = mn / avg;
-      T sg = T(0.05) * (T(1) - xi) / xi;
-      sg = tmin(sg, T(2));
-      sg = T(0.1) * sg * sg * sg;
-      mu = tmax(T(opt.mu_min), tmin(mu, sg * avg));
-    }
     bool ok = false;
     if (opt.hessian == 1) {
-      backward_sweep<M, T, TF, true>(w, pv, mu, T(opt.reg), so);
+      backward_sweep<M, T, TF, true>(w, pv, T(opt.reg), so);
       ok = so.ok;
     }
-    if (!ok) backward_sweep<M, T, TF, false>(w, pv, mu, T(opt.reg), so);
+    if (!ok) backward_sweep<M, T, TF, false>(w, pv, T(opt.reg), so);
     if (!so.finite || !so.ok) { info.exitflag = so.ok ? -6 : -5; break; }
     // ---- convergence test (IPOPT scaling of the dual residual)
     const T sd = tmax(T(100), so.mult_sum / T(N * (NH + NX))) / T(100);
+    res_comp = so.comp_max;
     if (so.res_stat / sd <= T(opt.tol_stat) && so.res_eq <= T(opt.tol_eq) && so.res_ineq <= T(opt.tol_ineq) &&
-        so.res_comp / sd <= T(opt.tol_comp)) {
+        so.comp_max / sd <= T(opt.tol_comp)) {
       info.exitflag = 1;
       break;
     }
     if (it == opt.max_iter) break;
+    // ---- monotone barrier update (Fiacco-McCormick as in IPOPT): shrink mu while the current barrier
+    //      problem is solved to within kappa_eps * mu
+    for (int rep = 0; rep < 8; ++rep) {
+      const T cmu = tmax(so.comp_max - mu, mu - so.comp_min);
+      const T emu = tmax(tmax(so.res_stat / sd, cmu / sd), tmax(so.res_eq, so.res_ineq));
+      if (emu <= T(10) * mu && mu > T(opt.mu_min)) {
+        const T m15 = mu * tsqrt(mu);
+        mu = tmax(T(opt.mu_min), tmin(T(0.2) * mu, m15));
+      } else break;
+    }
 
     // ---- forward roll-out of the Newton step; fraction-to-boundary step lengths; merit slope
     const T tau = tmax(T(0.99), T(1) - mu);
@@ -392,7 +405,7 @@ RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, co
         T du[NU];
         RMPC_UNROLL
         for (int j = 0; j < NU; ++j) {
-          T a = w.kff[k][j];
+          T a = w.kff0[k][j] + mu * w.kff1[k][j];
           RMPC_UNROLL
           for (int i = 0; i < NX; ++i) a += w.K[k][j * NX + i] * dx[i];
           du[j] = a;
@@ -474,6 +487,11 @@ RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, co
       if (!pole && (phi == phi) && phi <= phi0 + T(1e-4) * alpha * slope + tol_phi) { accepted = true; break; }
       alpha *= T(0.5);
     }
+#if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
+    printf("it %d mu %.3g f %.9g theta %.3g stat %.3g comp %.3g..%.3g | ap %.3g ad %.3g alpha %.3g dphi %.3g rho %.3g slope %.3g acc %d\n", it,
+           double(mu), double(so.f), double(so.theta), double(so.res_stat), double(so.comp_min), double(so.comp_max), double(ap), double(ad),
+           double(alpha), double(dphi), double(rho_pen), double(slope), int(accepted));
+#endif
     if (!accepted) { info.exitflag = -7; break; }
     // ---- take the step
     const T adu = tmin(ad, T(1));
@@ -497,7 +515,7 @@ RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, co
   info.res_stat = double(so.res_stat);
   info.res_eq = double(so.res_eq);
   info.res_ineq = double(so.res_ineq);
-  info.res_comp = double(so.res_comp);
+  info.res_comp = double(res_comp);
   info.mu = double(mu);
 }
 
