@@ -1,0 +1,177 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the oracle's golden
+solutions, against the oracle's KKT certificate, and against the host twin on the same seeded batches.
+Tolerances are north_star's: trajectory / first action within 1e-4 relative, objective within 1e-5 relative,
+equal constraint-satisfaction status."""
+import json
+import os
+
+import numpy as np
+import pytest
+import yaml
+
+from conftest import CONFIG, GOLDEN, SOLVERS
+from robot_mpcs_b200 import scenarios as sc
+
+pytestmark = pytest.mark.gpu
+
+GEN = {"point_robot_example": sc.point_robot_example, "point_robot_sweep": sc.point_robot_sweep, "boxer_radial": sc.boxer_radial,
+       "boxer_supermarket": sc.boxer_supermarket, "panda": sc.panda}
+FIXTURES = ["pointRobot_example", "pointRobot_sweep", "boxer_radial", "boxer_supermarket", "panda_example", "panda_jitter"]
+
+
+def _solver(sdir, B):
+    from robot_mpcs_b200.planner.solver import Solver
+    return Solver.from_directory(os.path.join(SOLVERS, sdir), device=0, max_batch=B)
+
+
+def _pm(sdir):
+    return yaml.safe_load(open(os.path.join(SOLVERS, sdir, "paramMap.yaml")))
+
+
+def _to_dev(s):
+    import torch
+    return {k: torch.as_tensor(v, device="cuda:0") for k, v in s.items()}
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_golden(built, name):
+    path = os.path.join(GOLDEN, name + ".json")
+    if not os.path.isfile(path):
+        pytest.skip("fixture not generated")
+    g = json.load(open(path))
+    s = GEN[g["generator"]](_pm(g["solver"]), **g["kwargs"])
+    d = _to_dev(s)
+    solver = _solver(g["solver"], d["xinit"].shape[0])
+    r = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    z = r["z"].cpu().numpy()
+    for case in g["cases"]:
+        b = case["index"]
+        zo = np.array(case["Z"])
+        assert int(r["exitflag"][b]) == 1, (name, b, int(r["exitflag"][b]))
+        rel = np.abs(z[b] - zo).max() / np.abs(zo).max()
+        assert rel < 1e-4, (name, b, rel)                                   # predicted trajectory, 1e-4 relative
+        nx = solver.nx
+        assert np.abs(z[b, 0, nx:] - zo[0, nx:]).max() <= 1e-4 * max(1.0, np.abs(zo[0, nx:]).max())  # first action
+        assert abs(float(r["obj"][b]) - case["obj"]) <= 1e-5 * abs(case["obj"])  # objective, 1e-5 relative
+        assert case["kkt"]["ineq"] < 1e-6  # oracle feasible <-> exitflag 1: equal constraint-satisfaction status
+
+
+@pytest.mark.parametrize("cfg,sdir,gen,B", [
+    ("pointRobotMpc.yaml", "pointRobot_n3_005_H20_noSlack", "point_robot_sweep", 512),
+    ("boxerRadialMpc.yaml", "boxer_n3_01_H30_noSlack", "boxer_radial", 256),
+    ("pandaMpc.yaml", "panda_n7_005_H20_noSlack", "panda", 64),
+    ("boxerSupermarketMpc.yaml", "boxer_n3_01_H40_noSlack", "boxer_supermarket", 128),
+])
+def test_batch_vs_twin_and_certificate(built, cfg, sdir, gen, B):
+    """Same seeded batch on the GPU and on the host twin: identical status, trajectories to 1e-6; then the oracle's
+    solver-independent KKT certificate on a few GPU solutions."""
+    from oracle.build_twin import Twin
+    from oracle.nlp import load_model
+    from oracle.solve import kkt_certificate
+    s = GEN[gen](_pm(sdir), B)
+    d = _to_dev(s)
+    solver = _solver(sdir, B)
+    r = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    z = r["z"].cpu().numpy()
+    ef = r["exitflag"].cpu().numpy()
+    tw = Twin(os.path.join(SOLVERS, sdir)).solve(s["xinit"], s["x0"], s["params"])
+    assert (ef == 1).mean() > 0.9
+    both = (ef == 1) & (tw["exitflag"] == 1)
+    assert (ef == tw["exitflag"]).mean() > 0.97          # fma contraction may flip a handful of hard cases
+    scale = np.abs(tw["z"][both]).max(axis=(1, 2))
+    err = np.abs(z[both] - tw["z"][both]).max(axis=(1, 2)) / scale
+    assert np.quantile(err, 0.99) < 1e-5, np.quantile(err, 0.99)
+    model = load_model(os.path.join(CONFIG, cfg))
+    for b in np.where(ef == 1)[0][:3]:
+        c = kkt_certificate(model, s["xinit"][b], s["params"][b].reshape(-1), z[b], act_tol=1e-5)
+        assert c["eq"] < 1e-6 and c["ineq"] < 1e-6 and c["stat"] < 1e-4, (b, c)
+
+
+def test_host_entry_point_and_reference_shaped_solve(built):
+    """rmpc_solve_batch_host (host pointers) and the forcespro-shaped Solver.solve(problem)."""
+    g = json.load(open(os.path.join(GOLDEN, "pointRobot_example.json")))
+    s = sc.point_robot_example(_pm(g["solver"]))
+    solver = _solver(g["solver"], 1)
+    out, exitflag, info = solver.solve({"xinit": s["xinit"][0], "x0": s["x0"][0].reshape(-1), "all_parameters": s["params"][0].reshape(-1)})
+    assert exitflag == 1 and sorted(out)[0] == "x01" and sorted(out)[-1] == "x20" and out["x01"].shape == (9,)
+    zo = np.array(g["Z"])
+    z = np.stack([out[k] for k in sorted(out)])
+    assert np.abs(z - zo).max() / np.abs(zo).max() < 1e-4
+    assert abs(info["obj"] - g["obj"]) < 1e-5 * g["obj"]
+
+
+def test_planner_api_reference_shaped(built):
+    """MPCPlanner with the reference's call sequence (examples/mpc_example.py:63-119, pointRobot_example.py:81-89)."""
+    from robot_mpcs_b200.planner.mpcPlanner import MPCPlanner, SolverDoesNotExistError
+    from robot_mpcs_b200.utils.utils import parse_setup
+    setup = parse_setup(os.path.join(CONFIG, "pointRobotMpc.yaml"))
+    with pytest.raises(SolverDoesNotExistError):
+        MPCPlanner("pointRobot", "/nonexistent/", **setup["mpc"])
+    pl = MPCPlanner("pointRobot", SOLVERS + os.sep, **setup["mpc"])
+    pl.concretize()
+    pl.reset()
+
+    class Obst:
+        def position(self): return [4.0, -0.5, 0.0]
+        def radius(self): return 1.0
+        def dimension(self): return 3
+    pl.setRadialConstraints([Obst()], 0.3)
+    pl.setSelfCollisionAvoidanceConstraints(0.3)
+    pl.setJointLimits(np.array([[-10, -10, -10], [10, 10, 10]]))
+    pl.setInputLimits(np.array([[-1, -1, -15], [1, 1, 15]]))
+    pl.setGoalReaching([8.2, -0.2])
+    pl.setConstraintAvoidance()
+    s = sc.point_robot_example(_pm("pointRobot_n3_005_H20_noSlack"))
+    assert np.allclose(pl._params, s["params"][0].reshape(-1))       # same buffer the scenario generator builds
+    action, output, exitflag = pl.computeAction(np.zeros(3), np.array([0.1, 0, 0]))
+    g = json.load(open(os.path.join(GOLDEN, "pointRobot_example.json")))
+    assert exitflag == 1 and action.shape == (3,)
+    assert np.allclose(action, np.array(g["Z"])[0, 6:9], atol=1e-4)
+    assert np.allclose(output["x02"], np.array(g["Z"])[1], atol=1e-4)
+
+
+def test_shift_and_set_params_kernels(built):
+    import torch
+    solver = _solver("boxer_n3_01_H10_noSlack", 33)
+    g = torch.Generator(device="cuda:0").manual_seed(0)
+    z = torch.rand(33, solver.N, solver.nvar, dtype=torch.float64, device="cuda:0", generator=g)
+    x0 = solver.shift_horizon(z)
+    ref = torch.cat([z[:, 1:], z[:, -1:]], 1)
+    assert torch.equal(x0, ref)
+    z2 = z.clone()
+    solver.shift_horizon(z2, z2)
+    assert torch.equal(z2, ref)
+    P = torch.zeros(33, solver.N, solver.npar, dtype=torch.float64, device="cuda:0")
+    v = torch.rand(33, 3, dtype=torch.float64, device="cuda:0", generator=g)
+    solver.set_params(P, [17, 18, 19], v)
+    assert torch.equal(P[:, :, 17:20], v[:, None, :].expand(-1, solver.N, -1)) and float(P[:, :, :17].abs().sum()) == 0
+    vs = torch.rand(33, solver.N, 4, dtype=torch.float64, device="cuda:0", generator=g)
+    solver.set_params(P, [1, 2, 3, 4], vs)
+    assert torch.equal(P[:, :, 1:5], vs)
+
+
+def test_full_size_properties(built):
+    """BASELINE config 2 at full size (B=4096): size-independent properties of every converged solution —
+    dynamics defect, inequality feasibility, initial state, and determinism (same inputs -> same bits)."""
+    import torch
+    from oracle.nlp import load_model
+    sdir = "boxer_n3_01_H30_noSlack"
+    B = 4096
+    s = sc.boxer_radial(_pm(sdir), B)
+    d = _to_dev(s)
+    solver = _solver(sdir, B)
+    r = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    r2 = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    assert torch.equal(r["z"], r2["z"]) and torch.equal(r["exitflag"], r2["exitflag"])
+    ef = r["exitflag"].cpu().numpy()
+    assert (ef == 1).mean() > 0.95
+    ok = torch.as_tensor(ef == 1)
+    m = load_model(os.path.join(CONFIG, "boxerRadialMpc.yaml"))
+    Z = r["z"].cpu()[ok]
+    Pm = torch.as_tensor(s["params"])[ok]
+    X, U = Z[:, :, : m.nx], Z[:, :, m.nx:]
+    assert float((X[:, 0] - torch.as_tensor(s["xinit"])[ok]).abs().max()) == 0.0
+    defect = (X[:, 1:] - m.step(X[:, :-1], U[:, :-1])).abs().max()
+    assert float(defect) < 1e-7
+    assert float(m.ineq(Z, Pm).min()) > -1e-7
+    assert float(Z.abs().max()) <= 100.0          # the +-100 box of the NLP is inactive, hence satisfied
