@@ -51,13 +51,13 @@ const char* twin_name() { return M::NAME; }
 void twin_dims(int* d) { d[0] = M::N; d[1] = M::NX; d[2] = M::NU; d[3] = M::NVAR; d[4] = M::NPAR; d[5] = M::NH; }
 int twin_max_threads() { return omp_get_max_threads(); }
 
-// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg]; precision: 0 f64, 1 f64+f32 factor, 2 f32
+// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg, max_inner]; precision: 0 f64, 1 f64+f32 factor, 2 f32
 int twin_solve_batch(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
                      int* iters, double* resid, const double* opts, int nthreads, int precision) {
   rmpc::Options o = rmpc::default_options();
   if (opts) {
     o.max_iter = int(opts[0]); o.hessian = int(opts[1]); o.tol_stat = opts[2]; o.tol_eq = opts[3]; o.tol_ineq = opts[4];
-    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8];
+    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8]; o.max_inner = int(opts[9]);
   }
   if (nthreads > 0) omp_set_num_threads(nthreads);
   if (precision == 0) run<double, double>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);

@@ -29,14 +29,15 @@ struct Options {
   double tol_comp;     // complementarity s*lambda
   double mu0;          // initial barrier parameter
   double mu_min;
-  double reg;          // Levenberg term added to the input block of every stage Hessian
+  double reg;          // Levenberg term added to the diagonal of every stage Hessian
+  int max_inner;       // force a barrier decrease after this many iterations at one mu (0: never)
 };
 
 RMPC_HD Options default_options() {
   Options o;
   o.max_iter = 200; o.hessian = 1;
   o.tol_stat = 1e-6; o.tol_eq = 1e-8; o.tol_ineq = 1e-8; o.tol_comp = 1e-8;
-  o.mu0 = 1.0; o.mu_min = 1e-11; o.reg = 0.0;
+  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.max_inner = 0;
   return o;
 }
 
@@ -229,7 +230,7 @@ RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T reg, SweepO
     RMPC_UNROLL
     for (int r = 0; r < M::NLIM; ++r) Q[M::lim_var(r) * NV + M::lim_var(r)] += sig[M::lim_row(r)];
     RMPC_UNROLL
-    for (int j = 0; j < NU; ++j) Q[(NX + j) * NV + NX + j] += reg;
+    for (int j = 0; j < NV; ++j) Q[j * NV + j] += reg;
     T qt0[NV], qt1[NV], gl[NV];
     RMPC_UNROLL
     for (int i = 0; i < NV; ++i) { qt0[i] = sd.g[i]; gl[i] = sd.g[i]; qt1[i] = T(0); }
@@ -365,14 +366,25 @@ RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, co
   int it = 0;
   SweepOut<M, T> so;
   T res_comp = T(0);
+  int inner = 0;
   for (; it <= opt.max_iter; ++it) {
     bool ok = false;
     if (opt.hessian == 1) {
       backward_sweep<M, T, TF, true>(w, pv, T(opt.reg), so);
       ok = so.ok;
     }
-    if (!ok) backward_sweep<M, T, TF, false>(w, pv, T(opt.reg), so);
+    if (!ok) {
+      // Gauss-Newton Hessian; if rounding still breaks positive definiteness (huge barrier weights), add a
+      // growing Levenberg term
+      T reg = T(opt.reg);
+      for (int tries = 0; tries < 4; ++tries) {
+        backward_sweep<M, T, TF, false>(w, pv, reg, so);
+        if (so.ok) break;
+        reg = tmax(reg * T(100), T(1e-6));
+      }
+    }
     if (!so.finite || !so.ok) { info.exitflag = so.ok ? -6 : -5; break; }
+    if (so.comp_max > T(1e15)) { info.exitflag = -7; break; }  // multipliers diverge: locally infeasible
     // ---- convergence test (IPOPT scaling of the dual residual)
     const T sd = tmax(T(100), so.mult_sum / T(N * (NH + NX))) / T(100);
     res_comp = so.comp_max;
@@ -384,10 +396,13 @@ RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, co
     if (it == opt.max_iter) break;
     // ---- monotone barrier update (Fiacco-McCormick as in IPOPT): shrink mu while the current barrier
     //      problem is solved to within kappa_eps * mu
+    ++inner;
     for (int rep = 0; rep < 8; ++rep) {
       const T cmu = tmax(so.comp_max - mu, mu - so.comp_min);
       const T emu = tmax(tmax(so.res_stat / sd, cmu / sd), tmax(so.res_eq, so.res_ineq));
-      if (emu <= T(10) * mu && mu > T(opt.mu_min)) {
+      const bool force = opt.max_inner > 0 && inner > opt.max_inner && rep == 0;
+      if ((emu <= T(10) * mu || force) && mu > T(opt.mu_min)) {
+        inner = 0;
         const T m15 = mu * tsqrt(mu);
         mu = tmax(T(opt.mu_min), tmin(T(0.2) * mu, m15));
       } else break;

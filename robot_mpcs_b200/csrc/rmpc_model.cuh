@@ -559,4 +559,57 @@ RMPC_HD void dyn_derivatives(const T* z, T* xn, T* AB, const T* nu, T* Q) {
   }
 }
 
+// Entry (i,j) of the Jacobian [A B] for the rows that do not depend on z (all rows for the double integrator,
+// rows 2..7 for the diff-drive model, whose rows 0,1 carry the cos/sin sums).
+template <class M, class T>
+RMPC_HD T dyn_const_entry(int i, int j) {
+  const T dt = T(M::DT);
+  if (M::BASE == 0) {
+    if (i < M::NQ) {
+      if (j == i) return T(1);
+      if (j == M::NQ + i) return dt;
+      if (j == M::NX + i) return T(0.5) * dt * dt;
+      return T(0);
+    }
+    if (j == i) return T(1);
+    if (j == M::NX + (i - M::NQ)) return dt;
+    return T(0);
+  }
+  if (j == i) return T(1);
+  if (i == 2) return j == 7 ? dt : (j == 9 ? T(0.5) * dt * dt : T(0));
+  if (i == 6) return j == 8 ? dt : T(0);
+  if (i == 7) return j == 9 ? dt : T(0);
+  return T(0);
+}
+template <class M> struct DynRows { static constexpr int NVR = (M::BASE == 0) ? 0 : 2; };  // z-dependent rows of [A B]
+
+// diff-drive only: nu-weighted second derivative of Phi over the variables (th, om, u1, v, u0) = z[2,7,9,6,8]
+template <class M, class T>
+RMPC_HD void dyn_curvature(const T* z, const T* nu, T Hc[5][5]) {
+  const T h = T(M::DT) / T(5);
+  const T th = z[2], v = z[6], om = z[7], u0 = z[8], u1 = z[9];
+  RMPC_UNROLL
+  for (int i = 0; i < 5; ++i)
+    RMPC_UNROLL
+    for (int j = 0; j < 5; ++j) Hc[i][j] = T(0);
+  RMPC_UNROLL
+  for (int j = 0; j < 5; ++j) {
+    const T a = (T(j) + T(0.5)) * h, b = T(0.5) * T(j) * (T(j) + T(1)) * h * h;
+    T s, c;
+    tsincos(th + a * om + b * u1, &s, &c);
+    const T w = v + a * u0;
+    const T gp[3] = {T(1), a, b};
+    const T gw[2] = {T(1), a};
+    const T cpp = h * w * (-nu[0] * c - nu[1] * s);
+    const T cpw = h * (-nu[0] * s + nu[1] * c);
+    RMPC_UNROLL
+    for (int i = 0; i < 3; ++i) {
+      RMPC_UNROLL
+      for (int l = 0; l < 3; ++l) Hc[i][l] += cpp * gp[i] * gp[l];
+      RMPC_UNROLL
+      for (int l = 0; l < 2; ++l) { Hc[i][3 + l] += cpw * gp[i] * gw[l]; Hc[3 + l][i] += cpw * gp[i] * gw[l]; }
+    }
+  }
+}
+
 }  // namespace rmpc
