@@ -15,25 +15,28 @@
 
 using M = ModelTraits;
 
-template <class T, class TF>
+template <class T>
 static void run(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
                 int* iters, double* resid, const rmpc::Options& opt) {
 #pragma omp parallel
   {
-    auto* w = new rmpc::Work<M, T>();
+    auto* S = new rmpc::ProblemShared<M, T>();
     T* p = new T[M::N * M::NPAR];
+    T* zin = new T[M::N * M::NVAR];
+    T* zo = new T[M::N * M::NVAR];
+    rmpc::Group<1> g{0};
 #pragma omp for schedule(dynamic, 8)
     for (int b = 0; b < B; ++b) {
-      for (int k = 0; k < M::N; ++k)
-        for (int i = 0; i < M::NVAR; ++i) w->z[k][i] = T(x0[(size_t(b) * M::N + k) * M::NVAR + i]);
+      for (int i = 0; i < M::N * M::NVAR; ++i) zin[i] = T(x0[size_t(b) * M::N * M::NVAR + i]);
       for (int i = 0; i < M::N * M::NPAR; ++i) p[i] = T(params[size_t(b) * M::N * M::NPAR + i]);
       T xi[M::NX];
       for (int i = 0; i < M::NX; ++i) xi[i] = T(xinit[size_t(b) * M::NX + i]);
       rmpc::ParamView<T> pv{p, M::NPAR, 1};
       rmpc::Info info;
-      rmpc::solve_one<M, T, TF>(*w, xi, pv, opt, info);
-      for (int k = 0; k < M::N; ++k)
-        for (int i = 0; i < M::NVAR; ++i) z_out[(size_t(b) * M::N + k) * M::NVAR + i] = double(w->z[k][i]);
+      auto* ipm = new rmpc::Ipm<M, T, 1>(g, *S, pv, opt);
+      ipm->solve(xi, zin, zo, info);
+      delete ipm;
+      for (int i = 0; i < M::N * M::NVAR; ++i) z_out[size_t(b) * M::N * M::NVAR + i] = double(zo[i]);
       exitflag[b] = info.exitflag;
       iters[b] = info.iters;
       if (resid) {
@@ -41,8 +44,8 @@ static void run(int B, const double* xinit, const double* x0, const double* para
         r[0] = info.obj; r[1] = info.res_stat; r[2] = info.res_eq; r[3] = info.res_ineq; r[4] = info.res_comp; r[5] = info.mu;
       }
     }
-    delete w;
-    delete[] p;
+    delete S;
+    delete[] p; delete[] zin; delete[] zo;
   }
 }
 
@@ -51,18 +54,17 @@ const char* twin_name() { return M::NAME; }
 void twin_dims(int* d) { d[0] = M::N; d[1] = M::NX; d[2] = M::NU; d[3] = M::NVAR; d[4] = M::NPAR; d[5] = M::NH; }
 int twin_max_threads() { return omp_get_max_threads(); }
 
-// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg, max_inner]; precision: 0 f64, 1 f64+f32 factor, 2 f32
+// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg, delta, kappa, tau_min]; precision: 0 f64, 2 f32
 int twin_solve_batch(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
                      int* iters, double* resid, const double* opts, int nthreads, int precision) {
   rmpc::Options o = rmpc::default_options();
   if (opts) {
     o.max_iter = int(opts[0]); o.hessian = int(opts[1]); o.tol_stat = opts[2]; o.tol_eq = opts[3]; o.tol_ineq = opts[4];
-    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8]; o.max_inner = int(opts[9]);
+    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8]; o.delta = opts[9]; o.kappa = opts[10]; o.tau_min = opts[11]; o.lm0 = opts[12]; o.lm_up = opts[13]; o.lm_down = opts[14]; o.lm_trigger = opts[15];
   }
   if (nthreads > 0) omp_set_num_threads(nthreads);
-  if (precision == 0) run<double, double>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
-  else if (precision == 1) run<double, float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
-  else run<float, float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
+  if (precision == 2) run<float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
+  else run<double>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
   return 0;
 }
 
@@ -74,14 +76,15 @@ void twin_stage_values(const double* z, const double* p, double* f, double* h) {
   for (int i = 0; i < M::NH; ++i) h[i] = sv.h[i];
 }
 void twin_dynamics(const double* z, double* xn, double* AB) {
-  rmpc::dyn_derivatives<M, double, false>(z, xn, AB, nullptr, nullptr);
+  double ABv[rmpc::DynS<M>::NABV], Hc[5][5];
+  rmpc::dyn_eval<M, double>(z, xn, ABv, false, 0.0, 0.0, Hc);
+  rmpc::dyn_dense<M, double>(ABv, AB);
 }
 // exact: Hqq includes rho/kappa terms; returns cost grad g[NVAR], Hqq[NQ*NQ], Hd[NVAR], h[NH], Gg[NGEO*NQ]
 void twin_stage_derivatives(const double* z, const double* p, const double* rho, const double* kappa, int exact,
                             double* f, double* g, double* Hqq, double* Hd, double* h, double* Gg) {
   rmpc::StageDer<M, double> sd;
-  if (exact) rmpc::stage_derivatives<M, double, true>(z, p, rho, kappa, sd);
-  else rmpc::stage_derivatives<M, double, false>(z, p, rho, kappa, sd);
+  rmpc::stage_derivatives<M, double>(z, p, rho, kappa, exact != 0, sd);
   *f = sd.f;
   for (int i = 0; i < M::NVAR; ++i) { g[i] = sd.g[i]; Hd[i] = sd.Hd[i]; }
   for (int i = 0; i < M::NQ * M::NQ; ++i) Hqq[i] = sd.Hqq[i];
@@ -89,8 +92,12 @@ void twin_stage_derivatives(const double* z, const double* p, const double* rho,
   for (int r = 0; r < M::NGEO; ++r)
     for (int i = 0; i < M::NQ; ++i) Gg[r * M::NQ + i] = sd.Gg[r][i];
 }
+// Q (NVAR x NVAR, row-major) += nu-weighted second derivative of Phi (diff-drive only; a no-op otherwise)
 void twin_dyn_curvature(const double* z, const double* nu, double* Q) {
-  double xn[M::NX], AB[M::NX * M::NVAR];
-  rmpc::dyn_derivatives<M, double, true>(z, xn, AB, nu, Q);
+  double xn[M::NX], ABv[rmpc::DynS<M>::NABV], Hc[5][5];
+  rmpc::dyn_eval<M, double>(z, xn, ABv, true, nu[0], nu[1], Hc);
+  if (M::BASE == 1)
+    for (int a = 0; a < 5; ++a)
+      for (int b = 0; b < 5; ++b) Q[rmpc::DynS<M>::vc(a) * M::NVAR + rmpc::DynS<M>::vc(b)] += Hc[a][b];
 }
 }

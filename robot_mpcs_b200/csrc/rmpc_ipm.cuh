@@ -1,21 +1,29 @@
-// rmpc_ipm.cuh — one nonlinear-MPC solve: primal-dual interior point on the stage-structured NLP
+// rmpc_ipm.cuh — one nonlinear-MPC solve, cooperatively by a group of G lanes.
 //
 //   min  sum_k J(z_k,p_k)   s.t.  x_1 = xinit,  x_{k+1} = Phi(x_k,u_k),  h(z_k,p_k) >= 0
 //
-// with slacks (h - s = 0, s >= 0), the inequality multipliers condensed into the stage Hessians and the
-// resulting equality-constrained QP solved by a backward Riccati recursion / forward roll-out.  This is
-// the component that replaces the FORCESPRO-generated solver the reference calls at
-// planner/mpcPlanner.py:262.  One *lane* runs one problem (a warp = 32 problems);
-// all per-problem state lives in a `Work` struct that the compiler places in registers / lane-interleaved
-// local memory, so that every access of a warp is coalesced.
+// This is the component that replaces the FORCESPRO-generated solver the reference calls at
+// planner/mpcPlanner.py:262.
 //
-// Precision: `T` is the iterate/residual type, `TF` the type of the Riccati factorisation (the O(n^3)
-// part).  (T,TF) = (double,double) is the reference-grade path, (double,float) the mixed path.
+// Algorithm: primal-dual interior point (log barrier) that stays strictly inside h + shift > 0, where the shift is
+// zero for every row that is strictly feasible at the initial guess and is driven to zero otherwise; the dynamics
+// are treated as equalities (infeasible start, l1 merit).  Per iteration
+//   A  stage-parallel   lane k evaluates stage k: cost gradient, Hessian (exact Lagrangian or Gauss-Newton),
+//                       inequality rows + Jacobians, dynamics value + sensitivities + defect
+//   B  backward sweep   Riccati recursion over the horizon; the G lanes share the small dense products of every
+//                       stage through shared memory (4 group barriers per stage); the adjoint recursion that gives
+//                       the stationarity residual rides along as an extra right-hand side.  The barrier parameter
+//                       enters only the gradient, so the vector recursion is carried twice (mu-independent part,
+//                       coefficient of mu) and mu is chosen after the sweep from the residuals it measured.
+//   C  roll-out         every lane runs the (cheap) forward recursion and keeps the step of the stage it owns
+//   D  line search      stage-parallel trial evaluations, group reductions, fraction-to-boundary on the true
+//                       nonlinear rows and Armijo on the l1 merit
+// With G = 1 the same code is the sequential host twin (oracle/cpu_twin.cpp); with G = 32 a warp solves one
+// problem (rmpc_solver.cu).
 #pragma once
 #include "rmpc_model.cuh"
 #if defined(RMPC_TRACE)
 #include <stdio.h>
-#include <stdlib.h>
 #endif
 
 namespace rmpc {
@@ -25,47 +33,70 @@ struct Options {
   int hessian;         // 0 Gauss-Newton, 1 exact Lagrangian Hessian with GN fallback when not positive definite
   double tol_stat;     // scaled stationarity
   double tol_eq;       // dynamics defect
-  double tol_ineq;     // |h - s|
+  double tol_ineq;     // remaining shift of rows that started infeasible
   double tol_comp;     // complementarity s*lambda
   double mu0;          // initial barrier parameter
   double mu_min;
   double reg;          // Levenberg term added to the diagonal of every stage Hessian
-  int max_inner;       // force a barrier decrease after this many iterations at one mu (0: never)
+  double delta;        // rows with h < delta at the initial guess start shifted to s = delta
+  double kappa;        // multipliers are kept above mu/(kappa s)
+  double tau_min;      // fraction-to-boundary parameter tau = max(tau_min, 1 - mu)
+  double lm0, lm_up, lm_down, lm_trigger;  // adaptive damping: start value, growth, decay, backtracks that trigger growth
 };
 
 RMPC_HD Options default_options() {
   Options o;
   o.max_iter = 200; o.hessian = 1;
   o.tol_stat = 1e-6; o.tol_eq = 1e-8; o.tol_ineq = 1e-8; o.tol_comp = 1e-8;
-  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.max_inner = 0;
+  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3;
   return o;
 }
 
 struct Info {
-  int exitflag;   // 1 optimal, 0 iteration limit, -6 NaN/Inf, -7 line search failed (FORCESPRO sign convention)
+  int exitflag;   // 1 optimal, 0 iteration limit, -5 factorisation, -6 NaN/Inf, -7 no progress / infeasible, -8 bad initial guess
   int iters;
   double obj, res_stat, res_eq, res_ineq, res_comp, mu;
 };
 
-template <class M, class T>
-struct Work {
-  T z[M::N][M::NVAR];
-  T s[M::N][M::NH];
-  T lam[M::N][M::NH];
-  T dz[M::N][M::NVAR];
-  T K[M::N][M::NU * M::NX];
-  T kff0[M::N][M::NU];                               // feed-forward, mu-independent part
-  T kff1[M::N][M::NU];                               // feed-forward, coefficient of mu
-  T gf[M::N][M::NVAR];                               // cost gradient
-  T hh[M::N][M::NH];                                 // h(z)
-  T Gg[M::N][M::NGEO > 0 ? M::NGEO : 1][M::NQ];      // geometric row gradients
+// ------------------------------------------------------------------------------------------------
+// Lane group: G lanes that own interleaved stages (lane l owns stages l, l+G, ...) and share `ProblemShared`.
+template <int G> struct Group;
+template <> struct Group<1> {
+  int lane;
+  RMPC_HD void sync() const {}
+  template <class T> RMPC_HD T sum(T v) const { return v; }
+  template <class T> RMPC_HD T max(T v) const { return v; }
+  template <class T> RMPC_HD T min(T v) const { return v; }
+  RMPC_HD bool any(bool p) const { return p; }
 };
+#if defined(__CUDACC__)
+template <> struct Group<32> {
+  int lane;
+  __device__ __forceinline__ void sync() const { __syncwarp(); }
+  template <class T> __device__ __forceinline__ T sum(T v) const {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+  }
+  template <class T> __device__ __forceinline__ T max(T v) const {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const T w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
+    return v;
+  }
+  template <class T> __device__ __forceinline__ T min(T v) const {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const T w = __shfl_xor_sync(0xffffffffu, v, o); v = w < v ? w : v; }
+    return v;
+  }
+  __device__ __forceinline__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
+};
+#endif
 
-// Parameter access: p(k, j) of the problem this lane owns.
+// Parameter access: p(k, j) of one problem.
 template <class T>
 struct ParamView {
   const T* base;
-  long stage_stride;  // elements between consecutive stages (0: stage-invariant)
+  long stage_stride;  // elements between consecutive stages
   long elem_stride;   // elements between consecutive parameters
   RMPC_HD T get(int k, int j) const { return base[k * stage_stride + j * elem_stride]; }
 };
@@ -76,462 +107,539 @@ RMPC_HD void load_params(const ParamView<T>& pv, int k, T* p) {
   for (int j = 0; j < M::NPAR; ++j) p[j] = pv.get(k, j);
 }
 
-// directional derivative of row r of stage k along dz_k
-template <class M, class T>
-RMPC_HD void row_dirs(const Work<M, T>& w, int k, T* gd) {
-  RMPC_UNROLL
-  for (int r = 0; r < M::NGEO; ++r) {
-    T a = T(0);
-    RMPC_UNROLL
-    for (int i = 0; i < M::NQ; ++i) a += w.Gg[k][r][i] * w.dz[k][i];
-    gd[M::geo_row(r)] = a;
-  }
-  RMPC_UNROLL
-  for (int r = 0; r < M::NLIM; ++r) gd[M::lim_row(r)] = T(M::lim_sign(r)) * w.dz[k][M::lim_var(r)];
-}
-
-// G' y for a stage (adds -G'y into out)
-template <class M, class T>
-RMPC_HD void sub_Gt(const Work<M, T>& w, int k, const T* y, T* out) {
-  RMPC_UNROLL
-  for (int r = 0; r < M::NGEO; ++r) {
-    const T yr = y[M::geo_row(r)];
-    RMPC_UNROLL
-    for (int i = 0; i < M::NQ; ++i) out[i] -= w.Gg[k][r][i] * yr;
-  }
-  RMPC_UNROLL
-  for (int r = 0; r < M::NLIM; ++r) out[M::lim_var(r)] -= T(M::lim_sign(r)) * y[M::lim_row(r)];
-}
-
-// Cholesky of the NU x NU block, then K = -Fuu^{-1} Fux and the two feed-forward vectors
-// kff0 = -Fuu^{-1} fu0 (mu-independent part of the gradient), kff1 = -Fuu^{-1} fu1 (coefficient of mu).
-// Returns false if a pivot is not positive (Hessian not positive definite on the null space of the dynamics).
-template <class M, class TF>
-RMPC_HD bool factor_solve(TF* Fuu, const TF* Fux, const TF* fu0, const TF* fu1, TF* K, TF* kff0, TF* kff1) {
-  constexpr int NU = M::NU, NX = M::NX;
-  RMPC_UNROLL
-  for (int j = 0; j < NU; ++j) {
-    TF d = Fuu[j * NU + j];
-    RMPC_UNROLL
-    for (int k = 0; k < j; ++k) d -= Fuu[j * NU + k] * Fuu[j * NU + k];
-    if (!(d > TF(0))) return false;
-    const TF l = tsqrt(d), il = TF(1) / l;
-    Fuu[j * NU + j] = il;  // store the reciprocal pivot
-    RMPC_UNROLL
-    for (int i = j + 1; i < NU; ++i) {
-      TF v = Fuu[i * NU + j];
-      RMPC_UNROLL
-      for (int k = 0; k < j; ++k) v -= Fuu[i * NU + k] * Fuu[j * NU + k];
-      Fuu[i * NU + j] = v * il;
-    }
-  }
-  RMPC_UNROLL
-  for (int c = 0; c < NX + 2; ++c) {
-    TF y[NU];
-    RMPC_UNROLL
-    for (int i = 0; i < NU; ++i) {
-      TF v = (c < NX) ? Fux[i * NX + (c < NX ? c : 0)] : (c == NX ? fu0[i] : fu1[i]);
-      RMPC_UNROLL
-      for (int k = 0; k < i; ++k) v -= Fuu[i * NU + k] * y[k];
-      y[i] = v * Fuu[i * NU + i];
-    }
-    RMPC_UNROLL
-    for (int i = NU - 1; i >= 0; --i) {
-      TF v = y[i];
-      RMPC_UNROLL
-      for (int k = i + 1; k < NU; ++k) v -= Fuu[k * NU + i] * y[k];
-      y[i] = v * Fuu[i * NU + i];
-    }
-    RMPC_UNROLL
-    for (int i = 0; i < NU; ++i) {
-      if (c < NX) K[i * NX + (c < NX ? c : 0)] = -y[i];
-      else if (c == NX) kff0[i] = -y[i];
-      else kff1[i] = -y[i];
-    }
-  }
-  return true;
-}
-
-template <class M, class T>
-struct SweepOut {
-  T res_stat, res_eq, res_ineq;
-  T comp_min, comp_max; // extrema of s*lambda
-  T f, theta, logs;     // objective, l1 infeasibility, sum log s
-  T mult_sum;           // |nu|_1 + |lam|_1
-  bool ok, pole, finite;
+// ------------------------------------------------------------------------------------------------
+// Shared (per problem) storage.  GPU: shared memory of the warp that owns the problem; host: heap.
+template <class M> struct Dims {
+  static constexpr int NDS = (M::BASE == 0) ? M::NQ : M::NVAR;   // variables coupled by the dense part of the stage Hessian
+  static constexpr int NQD = NDS * (NDS + 1) / 2;
+  static constexpr int NVA = M::NVAR + 3;                         // [A B]-sized blocks carry 3 extra columns: g0, g1, adjoint
 };
 
-// One backward sweep at the current iterate: model derivatives, adjoint multipliers + KKT residuals,
-// condensed stage QP, Riccati factorisation.  EXACT selects the Hessian.  The barrier parameter enters the
-// Newton system only through the gradient  -mu G'(1/s); the vector recursion is therefore carried twice
-// (mu-independent part and coefficient of mu) so that mu is chosen *after* the sweep, from the residuals
-// the sweep itself measured.
-template <class M, class T, class TF, bool EXACT>
-RMPC_HD void backward_sweep(Work<M, T>& w, const ParamView<T>& pv, T reg, SweepOut<M, T>& o) {
-  constexpr int NX = M::NX, NU = M::NU, NV = M::NVAR, NH = M::NH, N = M::N;
-  TF P[NX * NX], p0[NX], p1[NX];
-  T nu[NX];
-  RMPC_UNROLL
-  for (int i = 0; i < NX * NX; ++i) P[i] = TF(0);
-  RMPC_UNROLL
-  for (int i = 0; i < NX; ++i) { p0[i] = TF(0); p1[i] = TF(0); nu[i] = T(0); }
-  o.res_stat = o.res_eq = o.res_ineq = T(0);
-  o.comp_min = T(1e30); o.comp_max = T(0);
-  o.f = o.theta = o.logs = o.mult_sum = T(0);
-  o.ok = true; o.pole = false; o.finite = true;
+template <class M, class T>
+struct StageShared {
+  T z[M::NVAR];
+  T qt0[M::NVAR];            // cost gradient
+  T qt1[M::NVAR];            // -G' (1/s): coefficient of mu in the barrier gradient
+  T gl[M::NVAR];             // cost gradient - G' lambda
+  T Qd[Dims<M>::NQD];        // dense symmetric part of the Hessian over the first NDS variables (lower triangle)
+  T Hd[M::NVAR];             // diagonal part
+  T ABv[DynS<M>::NABV];      // z-dependent entries of [A B]
+  T d[M::NX];                // Phi(z_k) - x_{k+1}
+  T K[M::NU * M::NX];        // feedback gain
+  T kff0[M::NU], kff1[M::NU];
+  T nu01[2];                 // adjoint of (X+, Y+) from the previous sweep (diff-drive curvature)
+};
 
-  for (int k = N - 1; k >= 0; --k) {
-    T p[M::NPAR];
-    load_params<M, T>(pv, k, p);
-    T zk[NV];
-    RMPC_UNROLL
-    for (int i = 0; i < NV; ++i) zk[i] = w.z[k][i];
-    // --- barrier quantities
-    T sig[NH], y0[NH], y1[NH], lamk[NH];
-    T rho[M::NGEO > 0 ? M::NGEO : 1], kappa[M::NGEO > 0 ? M::NGEO : 1];
-    RMPC_UNROLL
-    for (int r = 0; r < NH; ++r) { lamk[r] = w.lam[k][r]; y1[r] = T(1) / w.s[k][r]; sig[r] = lamk[r] * y1[r]; }
-    RMPC_UNROLL
-    for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lamk[M::geo_row(r)]; }
-    StageDer<M, T> sd;
-    stage_derivatives<M, T, EXACT>(zk, p, rho, kappa, sd);
-    o.f += sd.f;
-    o.pole = o.pole || sd.pole;
-    RMPC_UNROLL
-    for (int r = 0; r < NH; ++r) {
-      const T sr = w.s[k][r];
-      const T rh = sd.h[r] - sr;
-      w.hh[k][r] = sd.h[r];
-      y0[r] = lamk[r] - sig[r] * sd.h[r];     // y = y0 + mu * y1
-      o.res_ineq = tmax(o.res_ineq, tabs(rh));
-      o.theta += tabs(rh);
-      o.comp_max = tmax(o.comp_max, sr * lamk[r]);
-      o.comp_min = tmin(o.comp_min, sr * lamk[r]);
-      o.logs += tlog(sr);
-      o.mult_sum += tabs(lamk[r]);
-    }
-    RMPC_UNROLL
-    for (int r = 0; r < M::NGEO; ++r)
-      RMPC_UNROLL
-      for (int i = 0; i < M::NQ; ++i) w.Gg[k][r][i] = sd.Gg[r][i];
-    RMPC_UNROLL
-    for (int i = 0; i < NV; ++i) w.gf[k][i] = sd.g[i];
+template <class M, class T>
+struct ProblemShared {
+  StageShared<M, T> st[M::N];
+  T P[M::NX * M::NX], p0[M::NX], p1[M::NX], nu[M::NX];
+  T PAB[M::NX * Dims<M>::NVA];
+  T F[M::NVAR * Dims<M>::NVA];
+};
 
-    // --- stage Hessian Q (NV x NV); QP gradient qt0 + mu*qt1 = grad f - G'(y0 + mu y1); Lagrangian gradient gl
-    T Q[NV * NV];
-    RMPC_UNROLL
-    for (int i = 0; i < NV * NV; ++i) Q[i] = T(0);
-    RMPC_UNROLL
-    for (int i = 0; i < M::NQ; ++i)
-      RMPC_UNROLL
-      for (int j = 0; j < M::NQ; ++j) Q[i * NV + j] = sd.Hqq[i * M::NQ + j];
-    RMPC_UNROLL
-    for (int i = 0; i < NV; ++i) Q[i * NV + i] += sd.Hd[i];
-    RMPC_UNROLL
-    for (int r = 0; r < M::NLIM; ++r) Q[M::lim_var(r) * NV + M::lim_var(r)] += sig[M::lim_row(r)];
-    RMPC_UNROLL
-    for (int j = 0; j < NV; ++j) Q[j * NV + j] += reg;
-    T qt0[NV], qt1[NV], gl[NV];
-    RMPC_UNROLL
-    for (int i = 0; i < NV; ++i) { qt0[i] = sd.g[i]; gl[i] = sd.g[i]; qt1[i] = T(0); }
-    sub_Gt<M, T>(w, k, y0, qt0);
-    sub_Gt<M, T>(w, k, y1, qt1);
-    sub_Gt<M, T>(w, k, lamk, gl);
+template <class T>
+struct Red {  // what phase A + the sweep measure at the current iterate
+  T f, theta, logs, res_eq, res_stat, comp_min, comp_max, mult_sum, shift_max, s_min;
+  bool pole, ok, finite;
+};
 
-    TF Fxx[NX * NX], Fux[NU * NX], Fuu[NU * NU], fx0[NX], fu0[NU], fx1[NX], fu1[NU];
-    if (k < N - 1) {
-      // --- dynamics to the next stage: defect d, Jacobian [A B], adjoint, curvature
-      T xn[NX], AB[NX * NV];
-      dyn_derivatives<M, T, EXACT>(zk, xn, AB, nu, Q);
-      T d[NX];
-      RMPC_UNROLL
-      for (int i = 0; i < NX; ++i) {
-        d[i] = xn[i] - w.z[k + 1][i];
-        o.res_eq = tmax(o.res_eq, tabs(d[i]));
-        o.theta += tabs(d[i]);
-        o.mult_sum += tabs(nu[i]);
-      }
-      // adjoint: gl += [A B]' nu_{k+1}
-      RMPC_UNROLL
-      for (int j = 0; j < NV; ++j) {
-        T a = T(0);
-        RMPC_UNROLL
-        for (int i = 0; i < NX; ++i) a += AB[i * NV + j] * nu[i];
-        gl[j] += a;
-      }
-      // Riccati products (factorisation precision TF)
-      TF Pd[NX];
-      RMPC_UNROLL
-      for (int i = 0; i < NX; ++i) {
-        TF a = p0[i];
-        RMPC_UNROLL
-        for (int j = 0; j < NX; ++j) a += P[i * NX + j] * TF(d[j]);
-        Pd[i] = a;
-      }
-      TF PAB[NX * NV];
-      RMPC_UNROLL
-      for (int i = 0; i < NX; ++i)
-        RMPC_UNROLL
-        for (int j = 0; j < NV; ++j) {
-          TF a = TF(0);
-          RMPC_UNROLL
-          for (int l = 0; l < NX; ++l) a += P[i * NX + l] * TF(AB[l * NV + j]);
-          PAB[i * NV + j] = a;
-        }
-      RMPC_UNROLL
-      for (int i = 0; i < NV; ++i) {
-        TF g0 = TF(qt0[i]), g1 = TF(qt1[i]);
-        RMPC_UNROLL
-        for (int l = 0; l < NX; ++l) { g0 += TF(AB[l * NV + i]) * Pd[l]; g1 += TF(AB[l * NV + i]) * p1[l]; }
-        if (i < NX) { fx0[i < NX ? i : 0] = g0; fx1[i < NX ? i : 0] = g1; }
-        else { fu0[i >= NX ? i - NX : 0] = g0; fu1[i >= NX ? i - NX : 0] = g1; }
-        RMPC_UNROLL
-        for (int j = 0; j <= i; ++j) {
-          TF a = TF(Q[i * NV + j]);
-          RMPC_UNROLL
-          for (int l = 0; l < NX; ++l) a += TF(AB[l * NV + i]) * PAB[l * NV + j];
-          if (i < NX) { Fxx[(i < NX ? i : 0) * NX + j] = a; Fxx[j * NX + (i < NX ? i : 0)] = a; }
-          else if (j < NX) Fux[(i >= NX ? i - NX : 0) * NX + j] = a;
-          else { Fuu[(i - NX) * NU + (j - NX)] = a; Fuu[(j - NX) * NU + (i - NX)] = a; }
-        }
-      }
-    } else {
-      RMPC_UNROLL
-      for (int i = 0; i < NV; ++i) {
-        if (i < NX) { fx0[i < NX ? i : 0] = TF(qt0[i]); fx1[i < NX ? i : 0] = TF(qt1[i]); }
-        else { fu0[i >= NX ? i - NX : 0] = TF(qt0[i]); fu1[i >= NX ? i - NX : 0] = TF(qt1[i]); }
-        RMPC_UNROLL
-        for (int j = 0; j <= i; ++j) {
-          const TF a = TF(Q[i * NV + j]);
-          if (i < NX) { Fxx[(i < NX ? i : 0) * NX + j] = a; Fxx[j * NX + (i < NX ? i : 0)] = a; }
-          else if (j < NX) Fux[(i >= NX ? i - NX : 0) * NX + j] = a;
-          else { Fuu[(i - NX) * NU + (j - NX)] = a; Fuu[(j - NX) * NU + (i - NX)] = a; }
-        }
-      }
-    }
-    // stationarity residual (inputs) and adjoint for the next (earlier) stage
-    RMPC_UNROLL
-    for (int j = 0; j < NU; ++j) o.res_stat = tmax(o.res_stat, tabs(gl[NX + j]));
-    RMPC_UNROLL
-    for (int i = 0; i < NX; ++i) nu[i] = gl[i];
+// ------------------------------------------------------------------------------------------------
+template <class M, class T, int G>
+struct Ipm {
+  static constexpr int NX = M::NX, NU = M::NU, NV = M::NVAR, NH = M::NH, N = M::N, NQ = M::NQ;
+  static constexpr int NGEO1 = M::NGEO > 0 ? M::NGEO : 1;
+  static constexpr int SLOTS = (N + G - 1) / G;
+  static constexpr int NVA = Dims<M>::NVA, NDS = Dims<M>::NDS;
+  using DS = DynS<M>;
 
-    TF Kk[NU * NX], kf0[NU], kf1[NU];
-    if (!factor_solve<M, TF>(Fuu, Fux, fu0, fu1, Kk, kf0, kf1)) { o.ok = false; return; }
-    RMPC_UNROLL
-    for (int i = 0; i < NU * NX; ++i) w.K[k][i] = T(Kk[i]);
-    RMPC_UNROLL
-    for (int i = 0; i < NU; ++i) { w.kff0[k][i] = T(kf0[i]); w.kff1[k][i] = T(kf1[i]); }
-    // P_k = Fxx + Fux' K ,  p_k = fx + Fux' kff
-    RMPC_UNROLL
-    for (int i = 0; i < NX; ++i) {
-      TF a0 = fx0[i], a1 = fx1[i];
-      RMPC_UNROLL
-      for (int l = 0; l < NU; ++l) { a0 += Fux[l * NX + i] * kf0[l]; a1 += Fux[l * NX + i] * kf1[l]; }
-      p0[i] = a0; p1[i] = a1;
-      RMPC_UNROLL
-      for (int j = 0; j <= i; ++j) {
-        TF v = Fxx[i * NX + j];
-        RMPC_UNROLL
-        for (int l = 0; l < NU; ++l) v += Fux[l * NX + i] * Kk[l * NX + j];
-        P[i * NX + j] = v;
-        P[j * NX + i] = v;
-      }
-    }
-  }
-  o.finite = (o.f == o.f) && (o.res_stat == o.res_stat) && (o.theta == o.theta);
-}
+  const Group<G>& g;
+  ProblemShared<M, T>& S;
+  const ParamView<T>& pv;
+  const Options& opt;
 
-// -------------------------------------------------------------------------------------------------
-template <class M, class T, class TF>
-RMPC_HD void solve_one(Work<M, T>& w, const T* xinit, const ParamView<T>& pv, const Options& opt, Info& info) {
-  constexpr int NX = M::NX, NU = M::NU, NV = M::NVAR, NH = M::NH, N = M::N;
-  T mu = T(opt.mu0);
-  // ---- initial point: x_1 = xinit; slacks from h(z0); lambda = mu / s
-  RMPC_UNROLL
-  for (int i = 0; i < NX; ++i) w.z[0][i] = xinit[i];
-  for (int k = 0; k < N; ++k) {
-    T p[M::NPAR];
-    load_params<M, T>(pv, k, p);
-    StageVal<M, T> sv;
-    stage_values<M, T>(w.z[k], p, sv);
-    RMPC_UNROLL
-    for (int r = 0; r < NH; ++r) {
-      const T sr = tmax(sv.h[r], T(1e-2));
-      w.s[k][r] = sr;
-      w.lam[k][r] = mu / sr;
-    }
-  }
-  T rho_pen = T(1);
-  info.exitflag = 0;
-  int it = 0;
-  SweepOut<M, T> so;
-  T res_comp = T(0);
-  int inner = 0;
-  for (; it <= opt.max_iter; ++it) {
-    bool ok = false;
-    if (opt.hessian == 1) {
-      backward_sweep<M, T, TF, true>(w, pv, T(opt.reg), so);
-      ok = so.ok;
-    }
-    if (!ok) {
-      // Gauss-Newton Hessian; if rounding still breaks positive definiteness (huge barrier weights), add a
-      // growing Levenberg term
-      T reg = T(opt.reg);
-      for (int tries = 0; tries < 4; ++tries) {
-        backward_sweep<M, T, TF, false>(w, pv, reg, so);
-        if (so.ok) break;
-        reg = tmax(reg * T(100), T(1e-6));
-      }
-    }
-    if (!so.finite || !so.ok) { info.exitflag = so.ok ? -6 : -5; break; }
-    if (so.comp_max > T(1e15)) { info.exitflag = -7; break; }  // multipliers diverge: locally infeasible
-    // ---- convergence test (IPOPT scaling of the dual residual)
-    const T sd = tmax(T(100), so.mult_sum / T(N * (NH + NX))) / T(100);
-    res_comp = so.comp_max;
-    if (so.res_stat / sd <= T(opt.tol_stat) && so.res_eq <= T(opt.tol_eq) && so.res_ineq <= T(opt.tol_ineq) &&
-        so.comp_max / sd <= T(opt.tol_comp)) {
-      info.exitflag = 1;
-      break;
-    }
-    if (it == opt.max_iter) break;
-    // ---- monotone barrier update (Fiacco-McCormick as in IPOPT): shrink mu while the current barrier
-    //      problem is solved to within kappa_eps * mu
-    ++inner;
-    for (int rep = 0; rep < 8; ++rep) {
-      const T cmu = tmax(so.comp_max - mu, mu - so.comp_min);
-      const T emu = tmax(tmax(so.res_stat / sd, cmu / sd), tmax(so.res_eq, so.res_ineq));
-      const bool force = opt.max_inner > 0 && inner > opt.max_inner && rep == 0;
-      if ((emu <= T(10) * mu || force) && mu > T(opt.mu_min)) {
-        inner = 0;
-        const T m15 = mu * tsqrt(mu);
-        mu = tmax(T(opt.mu_min), tmin(T(0.2) * mu, m15));
-      } else break;
-    }
+  // per-lane state of the stages this lane owns
+  T lam[SLOTS][NH], s[SLOTS][NH], sh[SLOTS][NH], htr[SLOTS][NH];
+  T Gg[SLOTS][NGEO1][NQ];
+  T dz[SLOTS][NV], dxn[SLOTS][NX];
 
-    // ---- forward roll-out of the Newton step; fraction-to-boundary step lengths; merit slope
-    const T tau = tmax(T(0.99), T(1) - mu);
-    T ap = T(1), ad = T(1);
-    T dphi = T(0);
-    {
-      T dx[NX];
-      RMPC_UNROLL
-      for (int i = 0; i < NX; ++i) dx[i] = T(0);  // x_1 is fixed
-      for (int k = 0; k < N; ++k) {
-        T du[NU];
+  RMPC_HD Ipm(const Group<G>& g_, ProblemShared<M, T>& S_, const ParamView<T>& pv_, const Options& o_) : g(g_), S(S_), pv(pv_), opt(o_) {}
+
+  static RMPC_HD int tri(int a, int b) { return a >= b ? a * (a + 1) / 2 + b : b * (b + 1) / 2 + a; }
+
+  // ---- A: stage-parallel derivatives ----------------------------------------------------------
+  RMPC_HD void derivs(const bool exact, const T reg, Red<T>& o) {
+    T f = T(0), theta = T(0), logs = T(0), res_eq = T(0), cmin = T(1e300), cmax = T(0), msum = T(0), shmax = T(0), smin = T(1e300);
+    bool pole = false;
+    RMPC_UNROLL
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      const int k = g.lane + G * sl;
+      if (k < N) {
+        StageShared<M, T>& st = S.st[k];
+        T p[M::NPAR];
+        load_params<M, T>(pv, k, p);
+        T zk[NV];
         RMPC_UNROLL
-        for (int j = 0; j < NU; ++j) {
-          T a = w.kff0[k][j] + mu * w.kff1[k][j];
-          RMPC_UNROLL
-          for (int i = 0; i < NX; ++i) a += w.K[k][j * NX + i] * dx[i];
-          du[j] = a;
-        }
-        RMPC_UNROLL
-        for (int i = 0; i < NX; ++i) w.dz[k][i] = dx[i];
-        RMPC_UNROLL
-        for (int j = 0; j < NU; ++j) w.dz[k][NX + j] = du[j];
-        RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) dphi += w.gf[k][i] * w.dz[k][i];
-        T gd[NH];
-        row_dirs<M, T>(w, k, gd);
+        for (int i = 0; i < NV; ++i) zk[i] = st.z[i];
+        T sig[NH], y1[NH];
+        T rho[NGEO1], kappa[NGEO1];
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
-          const T sr = w.s[k][r], lr = w.lam[k][r];
-          const T dsr = gd[r] + w.hh[k][r] - sr;
-          const T dlr = mu / sr - lr - (lr / sr) * dsr;
-          if (dsr < T(0)) ap = tmin(ap, -tau * sr / dsr);
-          if (dlr < T(0)) ad = tmin(ad, -tau * lr / dlr);
-          dphi -= mu * dsr / sr;
+          const T sr = s[sl][r], lr = lam[sl][r];
+          y1[r] = T(1) / sr;
+          sig[r] = lr * y1[r];
+          logs += tlog(sr);
+          cmax = tmax(cmax, sr * lr);
+          cmin = tmin(cmin, sr * lr);
+          msum += lr;
+          shmax = tmax(shmax, sh[sl][r]);
+          if (sh[sl][r] > T(0)) smin = tmin(smin, sr);  // slack of a row that is still shifted
         }
-        if (k < N - 1) {
-          // linearised dynamics: dx+ = [A B] dz + d
-          T xn[NX], AB[NX * NV];
-          T zk[NV];
+        RMPC_UNROLL
+        for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lam[sl][M::geo_row(r)]; }
+        StageDer<M, T> sd;
+        stage_derivatives<M, T>(zk, p, rho, kappa, exact, sd);
+        f += sd.f;
+        pole = pole || sd.pole;
+        RMPC_UNROLL
+        for (int r = 0; r < M::NGEO; ++r)
           RMPC_UNROLL
-          for (int i = 0; i < NV; ++i) zk[i] = w.z[k][i];
-          dyn_derivatives<M, T, false>(zk, xn, AB, (const T*)0, (T*)0);
+          for (int i = 0; i < NQ; ++i) Gg[sl][r][i] = sd.Gg[r][i];
+        // gradients: qt0 = g, qt1 = -G'(1/s), gl = g - G'lambda
+        T q1[NV], glv[NV];
+        RMPC_UNROLL
+        for (int i = 0; i < NV; ++i) { q1[i] = T(0); glv[i] = sd.g[i]; }
+        RMPC_UNROLL
+        for (int r = 0; r < M::NGEO; ++r) {
+          const T a1 = y1[M::geo_row(r)], al = lam[sl][M::geo_row(r)];
+          RMPC_UNROLL
+          for (int i = 0; i < NQ; ++i) { q1[i] -= sd.Gg[r][i] * a1; glv[i] -= sd.Gg[r][i] * al; }
+        }
+        RMPC_UNROLL
+        for (int r = 0; r < M::NLIM; ++r) {
+          q1[M::lim_var(r)] -= T(M::lim_sign(r)) * y1[M::lim_row(r)];
+          glv[M::lim_var(r)] -= T(M::lim_sign(r)) * lam[sl][M::lim_row(r)];
+          sd.Hd[M::lim_var(r)] += sig[M::lim_row(r)];
+        }
+        RMPC_UNROLL
+        for (int i = 0; i < NV; ++i) { st.qt0[i] = sd.g[i]; st.qt1[i] = q1[i]; st.gl[i] = glv[i]; st.Hd[i] = sd.Hd[i] + reg; }
+        // dense part of the Hessian
+        T Qd[Dims<M>::NQD];
+        RMPC_UNROLL
+        for (int i = 0; i < Dims<M>::NQD; ++i) Qd[i] = T(0);
+        RMPC_UNROLL
+        for (int a = 0; a < NQ; ++a)
+          RMPC_UNROLL
+          for (int b = 0; b <= a; ++b) Qd[a * (a + 1) / 2 + b] = sd.Hqq[a * NQ + b];
+        if (k < N - 1) {
+          T xn[NX], ABv[DS::NABV], Hc[5][5];
+          dyn_eval<M, T>(zk, xn, ABv, exact, st.nu01[0], st.nu01[1], Hc);
           RMPC_UNROLL
           for (int i = 0; i < NX; ++i) {
-            T a = xn[i] - w.z[k + 1][i];
+            const T di = xn[i] - S.st[k + 1].z[i];
+            st.d[i] = di;
+            theta += tabs(di);
+            res_eq = tmax(res_eq, tabs(di));
+          }
+          RMPC_UNROLL
+          for (int i = 0; i < DS::NVR * DS::NVC; ++i) st.ABv[i] = ABv[i];
+          if (M::BASE == 1 && exact) {
             RMPC_UNROLL
-            for (int j = 0; j < NV; ++j) a += AB[i * NV + j] * w.dz[k][j];
-            dx[i] = a;
+            for (int a = 0; a < 5; ++a)
+              RMPC_UNROLL
+              for (int b = 0; b < 5; ++b)
+                if (DS::vc(a) >= DS::vc(b)) Qd[DS::vc(a) * (DS::vc(a) + 1) / 2 + DS::vc(b)] += Hc[a][b];
+          }
+        }
+        RMPC_UNROLL
+        for (int i = 0; i < Dims<M>::NQD; ++i) st.Qd[i] = Qd[i];
+      }
+    }
+    o.f = g.sum(f); o.theta = g.sum(theta); o.logs = g.sum(logs); o.res_eq = g.max(res_eq);
+    o.comp_min = g.min(cmin); o.comp_max = g.max(cmax); o.mult_sum = g.sum(msum); o.shift_max = g.max(shmax); o.s_min = g.min(smin);
+    o.pole = g.any(pole);
+    g.sync();
+  }
+
+  // ---- B: backward Riccati sweep, shared by the lanes -------------------------------------------
+  RMPC_HD void sweep(Red<T>& o) {
+    for (int e = g.lane; e < NX * NX; e += G) S.P[e] = T(0);
+    for (int e = g.lane; e < NX; e += G) { S.p0[e] = T(0); S.p1[e] = T(0); S.nu[e] = T(0); }
+    g.sync();
+    T res_stat = T(0), nsum = T(0);
+    bool ok = true;
+    for (int k = N - 1; k >= 0; --k) {
+      StageShared<M, T>& st = S.st[k];
+      const bool dyn = k < N - 1;
+      // phase 1: PAB = P [A B | d-term | p1 | nu]
+      if (dyn) {
+        for (int i = g.lane; i < NX; i += G) {
+          T Pi[NX];
+          RMPC_UNROLL
+          for (int l = 0; l < NX; ++l) Pi[l] = S.P[i * NX + l];
+          RMPC_UNROLL
+          for (int j = 0; j < NV; ++j) {
+            T a = T(0);
+            RMPC_UNROLL
+            for (int e = 0; e < DS::n(j); ++e) a += DS::template val<T>(j, e, st.ABv) * Pi[DS::row(j, e)];
+            S.PAB[i * NVA + j] = a;
+          }
+          T a = S.p0[i];
+          RMPC_UNROLL
+          for (int l = 0; l < NX; ++l) a += Pi[l] * st.d[l];
+          S.PAB[i * NVA + NV] = a;
+          S.PAB[i * NVA + NV + 1] = S.p1[i];
+          S.PAB[i * NVA + NV + 2] = S.nu[i];
+        }
+        g.sync();
+      }
+      // phase 2: F = [Q | qt0 | qt1 | gl] + [A B]' PAB
+      for (int j = g.lane; j < NVA; j += G) {
+        RMPC_UNROLL
+        for (int i = 0; i < NV; ++i) {
+          T a;
+          if (j < NV) {
+            a = (i == j) ? st.Hd[i] : T(0);
+            if (i < NDS && j < NDS) a += st.Qd[tri(i, j)];
+          } else {
+            a = (j == NV) ? st.qt0[i] : (j == NV + 1 ? st.qt1[i] : st.gl[i]);
+          }
+          if (dyn) {
+            RMPC_UNROLL
+            for (int e = 0; e < DS::n(i); ++e) a += DS::template val<T>(i, e, st.ABv) * S.PAB[DS::row(i, e) * NVA + j];
+          }
+          S.F[i * NVA + j] = a;
+        }
+      }
+      g.sync();
+      // phase 3: Cholesky of Fuu (every lane, redundantly) and the NX+2 solves (one column per lane)
+      {
+        T L[NU * NU];
+        RMPC_UNROLL
+        for (int a = 0; a < NU; ++a)
+          RMPC_UNROLL
+          for (int b = 0; b <= a; ++b) L[a * NU + b] = S.F[(NX + a) * NVA + NX + b];
+        RMPC_UNROLL
+        for (int j = 0; j < NU; ++j) {
+          T dd = L[j * NU + j];
+          RMPC_UNROLL
+          for (int c = 0; c < j; ++c) dd -= L[j * NU + c] * L[j * NU + c];
+          if (!(dd > T(0))) { ok = false; dd = T(1); }
+          const T il = T(1) / tsqrt(dd);
+          L[j * NU + j] = il;  // reciprocal pivot
+          RMPC_UNROLL
+          for (int i = j + 1; i < NU; ++i) {
+            T v = L[i * NU + j];
+            RMPC_UNROLL
+            for (int c = 0; c < j; ++c) v -= L[i * NU + c] * L[j * NU + c];
+            L[i * NU + j] = v * il;
+          }
+        }
+        RMPC_UNROLL
+        for (int j = 0; j < NU; ++j) res_stat = tmax(res_stat, tabs(S.F[(NX + j) * NVA + NV + 2]));
+        for (int c = g.lane; c < NX + 2; c += G) {
+          const int col = c < NX ? c : NV + (c - NX);
+          T y[NU];
+          RMPC_UNROLL
+          for (int i = 0; i < NU; ++i) {
+            T v = S.F[(NX + i) * NVA + col];
+            RMPC_UNROLL
+            for (int l = 0; l < i; ++l) v -= L[i * NU + l] * y[l];
+            y[i] = v * L[i * NU + i];
+          }
+          RMPC_UNROLL
+          for (int i = NU - 1; i >= 0; --i) {
+            T v = y[i];
+            RMPC_UNROLL
+            for (int l = i + 1; l < NU; ++l) v -= L[l * NU + i] * y[l];
+            y[i] = v * L[i * NU + i];
+          }
+          RMPC_UNROLL
+          for (int i = 0; i < NU; ++i) {
+            if (c < NX) st.K[i * NX + c] = -y[i];
+            else if (c == NX) st.kff0[i] = -y[i];
+            else st.kff1[i] = -y[i];
           }
         }
       }
-    }
-    // ---- l1 merit: penalty update and backtracking line search on (z, s)
-    if (so.theta > T(1e-14)) {
-      const T need = dphi / (T(0.9) * so.theta);
-      if (need > rho_pen) rho_pen = need * T(1.1) + T(1e-3);
-    }
-    const T phi0 = so.f - mu * so.logs + rho_pen * so.theta;
-    const T slope = dphi - rho_pen * so.theta;
-    T alpha = ap;
-    bool accepted = false;
-    for (int ls = 0; ls < 30; ++ls) {
-      T f = T(0), theta = T(0), logs = T(0);
-      bool pole = false;
-      T xn[NX];
-      for (int k = 0; k < N; ++k) {
-        T p[M::NPAR];
-        load_params<M, T>(pv, k, p);
-        T zt[NV];
-        RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) zt[i] = w.z[k][i] + alpha * w.dz[k][i];
-        if (k > 0) {
+      g.sync();
+      // phase 4: P = Fxx + Fux' K, p = fx + Fux' kff, adjoint nu = x-part of the Lagrangian gradient
+      for (int e = g.lane; e < NX * NX + 3 * NX; e += G) {
+        if (e < NX * NX) {
+          const int i = e / NX, j = e - i * NX;
+          T v = S.F[i * NVA + j];
           RMPC_UNROLL
-          for (int i = 0; i < NX; ++i) theta += tabs(xn[i] - zt[i]);
+          for (int l = 0; l < NU; ++l) v += S.F[(NX + l) * NVA + i] * st.K[l * NX + j];
+          S.P[e] = v;
+        } else {
+          const int t = e - NX * NX, which = t / NX, i = t - which * NX;
+          if (which == 2) {
+            const T v = S.F[i * NVA + NV + 2];
+            S.nu[i] = v;
+            nsum += tabs(v);
+            if (k > 0 && i < 2) S.st[k - 1].nu01[i] = v;
+          } else {
+            T v = S.F[i * NVA + NV + which];
+            RMPC_UNROLL
+            for (int l = 0; l < NU; ++l) v += S.F[(NX + l) * NVA + i] * (which == 0 ? st.kff0[l] : st.kff1[l]);
+            if (which == 0) S.p0[i] = v; else S.p1[i] = v;
+          }
         }
-        StageVal<M, T> sv;
-        stage_values<M, T>(zt, p, sv);
-        f += sv.f;
-        pole = pole || sv.pole;
-        T gd[NH];
-        row_dirs<M, T>(w, k, gd);
-        RMPC_UNROLL
-        for (int r = 0; r < NH; ++r) {
-          const T sr = w.s[k][r];
-          const T st = sr + alpha * (gd[r] + w.hh[k][r] - sr);
-          theta += tabs(sv.h[r] - st);
-          logs += tlog(st);
-        }
-        if (k < N - 1) dyn_value<M, T>(zt, xn);
       }
-      const T phi = f - mu * logs + rho_pen * theta;
-      const T tol_phi = T(10) * T(sizeof(T) == 8 ? 2.2e-16 : 1.2e-7) * tabs(phi0);
-      if (!pole && (phi == phi) && phi <= phi0 + T(1e-4) * alpha * slope + tol_phi) { accepted = true; break; }
-      alpha *= T(0.5);
+      g.sync();
     }
-#if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
-    printf("it %d mu %.3g f %.9g theta %.3g stat %.3g comp %.3g..%.3g | ap %.3g ad %.3g alpha %.3g dphi %.3g rho %.3g slope %.3g acc %d\n", it,
-           double(mu), double(so.f), double(so.theta), double(so.res_stat), double(so.comp_min), double(so.comp_max), double(ap), double(ad),
-           double(alpha), double(dphi), double(rho_pen), double(slope), int(accepted));
-#endif
-    if (!accepted) { info.exitflag = -7; break; }
-    // ---- take the step
-    const T adu = tmin(ad, T(1));
-    for (int k = 0; k < N; ++k) {
-      T gd[NH];
-      row_dirs<M, T>(w, k, gd);
-      RMPC_UNROLL
-      for (int r = 0; r < NH; ++r) {
-        const T sr = w.s[k][r], lr = w.lam[k][r];
-        const T dsr = gd[r] + w.hh[k][r] - sr;
-        const T dlr = mu / sr - lr - (lr / sr) * dsr;
-        w.s[k][r] = sr + alpha * dsr;
-        w.lam[k][r] = lr + adu * dlr;
+    o.res_stat = res_stat;  // identical in every lane
+    o.mult_sum += g.sum(nsum);
+    o.ok = ok;
+    o.finite = (o.f == o.f) && (o.res_stat == o.res_stat) && (o.theta == o.theta) && (o.mult_sum == o.mult_sum);
+  }
+
+  // ---- C: forward roll-out (every lane runs it, keeps the step of its own stages) -------------------
+  RMPC_HD void rollout(const T mu) {
+    T dx[NX];
+    RMPC_UNROLL
+    for (int i = 0; i < NX; ++i) dx[i] = T(0);  // x_1 is fixed
+    RMPC_UNROLL
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      for (int kk = 0; kk < G; ++kk) {
+        const int k = kk + G * sl;
+        if (k >= N) break;
+        const StageShared<M, T>& st = S.st[k];
+        T dzk[NV];
+        RMPC_UNROLL
+        for (int i = 0; i < NX; ++i) dzk[i] = dx[i];
+        RMPC_UNROLL
+        for (int j = 0; j < NU; ++j) {
+          T a = st.kff0[j] + mu * st.kff1[j];
+          RMPC_UNROLL
+          for (int i = 0; i < NX; ++i) a += st.K[j * NX + i] * dx[i];
+          dzk[NX + j] = a;
+        }
+        if (k < N - 1) {
+          RMPC_UNROLL
+          for (int i = 0; i < NX; ++i) dx[i] = st.d[i];
+          RMPC_UNROLL
+          for (int j = 0; j < NV; ++j)
+            RMPC_UNROLL
+            for (int e = 0; e < DS::n(j); ++e) dx[DS::row(j, e)] += DS::template val<T>(j, e, st.ABv) * dzk[j];
+        }
+        if (kk == g.lane) {
+          RMPC_UNROLL
+          for (int i = 0; i < NV; ++i) dz[sl][i] = dzk[i];
+          RMPC_UNROLL
+          for (int i = 0; i < NX; ++i) dxn[sl][i] = dx[i];
+        }
       }
-      RMPC_UNROLL
-      for (int i = 0; i < NV; ++i) w.z[k][i] += alpha * w.dz[k][i];
     }
   }
-  info.iters = it;
-  info.obj = double(so.f);
-  info.res_stat = double(so.res_stat);
-  info.res_eq = double(so.res_eq);
-  info.res_ineq = double(so.res_ineq);
-  info.res_comp = double(res_comp);
-  info.mu = double(mu);
-}
+
+  RMPC_HD void row_dirs(int sl, T* gd) const {
+    RMPC_UNROLL
+    for (int r = 0; r < M::NGEO; ++r) {
+      T a = T(0);
+      RMPC_UNROLL
+      for (int i = 0; i < NQ; ++i) a += Gg[sl][r][i] * dz[sl][i];
+      gd[M::geo_row(r)] = a;
+    }
+    RMPC_UNROLL
+    for (int r = 0; r < M::NLIM; ++r) gd[M::lim_row(r)] = T(M::lim_sign(r)) * dz[sl][M::lim_var(r)];
+  }
+
+  // ---- the solve ----------------------------------------------------------------------------------
+  RMPC_HD void solve(const T* xinit, const T* z_in, T* z_out, Info& info) {
+    // initial point: z from the guess, x_1 = xinit
+    for (int e = g.lane; e < N * NV; e += G) S.st[e / NV].z[e % NV] = z_in[e];
+    g.sync();
+    for (int e = g.lane; e < NX; e += G) S.st[0].z[e] = xinit[e];
+    for (int e = g.lane; e < N; e += G) { S.st[e].nu01[0] = T(0); S.st[e].nu01[1] = T(0); }
+    g.sync();
+    T mu = T(opt.mu0);
+    bool pole0 = false;
+    RMPC_UNROLL
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      const int k = g.lane + G * sl;
+      if (k < N) {
+        T p[M::NPAR];
+        load_params<M, T>(pv, k, p);
+        StageVal<M, T> sv;
+        stage_values<M, T>(S.st[k].z, p, sv);
+        pole0 = pole0 || sv.pole;
+        RMPC_UNROLL
+        for (int r = 0; r < NH; ++r) {
+          const T hv = sv.h[r];
+          const T shift = hv >= T(opt.delta) ? T(0) : T(opt.delta) - hv;
+          sh[sl][r] = shift;
+          s[sl][r] = hv + shift;
+          lam[sl][r] = mu / (hv + shift);
+        }
+      }
+    }
+    info.exitflag = 0;
+    int it = 0;
+    Red<T> so;
+    so.f = so.res_stat = so.res_eq = so.comp_max = so.shift_max = T(0);
+    T rho_pen = T(1);
+    T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
+    if (g.any(pole0)) { info.exitflag = -8; it = opt.max_iter + 1; }
+    for (; it <= opt.max_iter; ++it) {
+      bool exact = opt.hessian == 1;
+      T reg = T(opt.reg) + lm;
+      for (int tries = 0; tries < 5; ++tries) {
+        derivs(exact, reg, so);
+        sweep(so);
+        if (so.ok) break;
+        if (exact) exact = false;                       // not positive definite: Gauss-Newton
+        else reg = tmax(reg * T(100), T(1e-6));         // rounding broke it (huge barrier weights): Levenberg
+      }
+      if (!so.finite || !so.ok) { info.exitflag = so.ok ? -6 : -5; break; }
+      if (so.comp_max > T(1e15) || so.s_min < T(1e-13)) { info.exitflag = -7; break; }  // multipliers diverge: locally infeasible
+      // ---- convergence test (IPOPT scaling of the dual residual)
+      const T sd = tmax(T(100), so.mult_sum / T(N * (NH + NX))) / T(100);
+      if (so.res_stat / sd <= T(opt.tol_stat) && so.res_eq <= T(opt.tol_eq) && so.shift_max <= T(opt.tol_ineq) &&
+          so.comp_max / sd <= T(opt.tol_comp)) {
+        info.exitflag = 1;
+        break;
+      }
+      if (it == opt.max_iter) break;
+      // ---- monotone barrier update (Fiacco-McCormick as in IPOPT): shrink mu while the current barrier
+      //      problem is solved to within kappa_eps * mu
+      for (int rep = 0; rep < 8; ++rep) {
+        const T cmu = tmax(so.comp_max - mu, mu - so.comp_min);
+        const T emu = tmax(tmax(so.res_stat / sd, cmu / sd), tmax(so.res_eq, so.shift_max));
+        if (emu <= T(10) * mu && mu > T(opt.mu_min)) {
+          const T m15 = mu * tsqrt(mu);
+          mu = tmax(T(opt.mu_min), tmin(T(0.2) * mu, m15));
+        } else break;
+      }
+      // ---- Newton step, linear step-length estimates, merit slope
+      rollout(mu);
+      const T tau = tmax(T(opt.tau_min), T(1) - mu);
+      T ap = T(1), ad = T(1), dphi = T(0);
+      RMPC_UNROLL
+      for (int sl = 0; sl < SLOTS; ++sl) {
+        const int k = g.lane + G * sl;
+        if (k < N) {
+          T gd[NH];
+          row_dirs(sl, gd);
+          RMPC_UNROLL
+          for (int i = 0; i < NV; ++i) dphi += S.st[k].qt0[i] * dz[sl][i];
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r) {
+            const T sr = s[sl][r], lr = lam[sl][r];
+            const T dsr = gd[r];
+            const T dlr = mu / sr - lr - (lr / sr) * dsr;
+            if (dsr < T(0)) ap = tmin(ap, -tau * sr / dsr);
+            if (dlr < T(0)) ad = tmin(ad, -tau * lr / dlr);
+            dphi -= mu * dsr / sr;
+          }
+        }
+      }
+      ap = g.min(ap); ad = g.min(ad); dphi = g.sum(dphi);
+      if (so.theta > T(1e-14)) {
+        const T need = dphi / (T(0.9) * so.theta);
+        if (need > rho_pen) rho_pen = need * T(1.1) + T(1e-3);
+      }
+      const T phi0 = so.f - mu * so.logs + rho_pen * so.theta;
+      const T slope = dphi - rho_pen * so.theta;
+      // ---- backtracking: stay inside h + shift >= (1 - tau) s on the true rows, Armijo on the l1 merit
+      T alpha = ap;
+      bool accepted = false;
+      int nls = 0;
+      for (int ls = 0; ls < 30; ++ls) {
+        T f = T(0), theta = T(0), logs = T(0);
+        bool bad = false;
+        RMPC_UNROLL
+        for (int sl = 0; sl < SLOTS; ++sl) {
+          const int k = g.lane + G * sl;
+          if (k < N) {
+            T p[M::NPAR];
+            load_params<M, T>(pv, k, p);
+            T zt[NV];
+            RMPC_UNROLL
+            for (int i = 0; i < NV; ++i) zt[i] = S.st[k].z[i] + alpha * dz[sl][i];
+            StageVal<M, T> sv;
+            stage_values<M, T>(zt, p, sv);
+            f += sv.f;
+            bad = bad || sv.pole;
+            RMPC_UNROLL
+            for (int r = 0; r < NH; ++r) {
+              const T stv = sv.h[r] + sh[sl][r];
+              htr[sl][r] = sv.h[r];
+              if (!(stv >= (T(1) - tau) * s[sl][r])) {
+                bad = true;
+#if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
+                if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(s[sl][r]), double(lam[sl][r]), double(stv), double(s[sl][r] + alpha * gd[r]), double(alpha)); }
+#endif
+              }
+              logs += tlog(tmax(stv, T(1e-300)));
+            }
+            if (k < N - 1) {
+              T xn[NX];
+              dyn_value<M, T>(zt, xn);
+              RMPC_UNROLL
+              for (int i = 0; i < NX; ++i) theta += tabs(xn[i] - (S.st[k + 1].z[i] + alpha * dxn[sl][i]));
+            }
+          }
+        }
+        f = g.sum(f); theta = g.sum(theta); logs = g.sum(logs);
+        bad = g.any(bad);
+        const T phi = f - mu * logs + rho_pen * theta;
+        const T tol_phi = T(10) * T(sizeof(T) == 8 ? 2.2e-16 : 1.2e-7) * tabs(phi0);
+#if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
+        if (RMPC_TRACE > 1) printf("    ls %d alpha %.3g f %.9g (f0 %.9g) theta %.4g (%.4g) barrier %.6g (%.6g) bad %d phi-phi0 %.4g\n", ls, double(alpha), double(f), double(so.f), double(theta), double(so.theta), double(-mu * logs), double(-mu * so.logs), int(bad), double(phi - phi0));
+#endif
+        if (!bad && (phi == phi) && phi <= phi0 + T(1e-4) * alpha * slope + tol_phi) { accepted = true; break; }
+        alpha *= T(0.5);
+        ++nls;
+      }
+#if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
+      printf("it %d mu %.3g f %.9g theta %.3g stat %.3g comp %.3g..%.3g shift %.3g | ap %.3g ad %.3g alpha %.3g dphi %.3g rho %.3g slope %.3g acc %d ex %d\n",
+             it, double(mu), double(so.f), double(so.theta), double(so.res_stat), double(so.comp_min), double(so.comp_max),
+             double(so.shift_max), double(ap), double(ad), double(alpha), double(dphi), double(rho_pen), double(slope), int(accepted), int(exact));
+#endif
+      if (!accepted) { info.exitflag = -7; break; }
+      if (nls >= int(opt.lm_trigger)) lm = tmax(lm * T(opt.lm_up), T(opt.lm0));
+      else if (nls == 0) lm = lm * T(opt.lm_down) < T(0.1) * T(opt.lm0) ? T(0) : lm * T(opt.lm_down);
+      // ---- take the step
+      g.sync();  // every lane has read its neighbour's z for this line search
+      const T adu = tmin(ad, T(1));
+      RMPC_UNROLL
+      for (int sl = 0; sl < SLOTS; ++sl) {
+        const int k = g.lane + G * sl;
+        if (k < N) {
+          T gd[NH];
+          row_dirs(sl, gd);
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r) {
+            const T sr = s[sl][r], lr = lam[sl][r];
+            const T dlr = mu / sr - lr - (lr / sr) * gd[r];
+            T sn = htr[sl][r] + sh[sl][r];
+            if (sh[sl][r] > T(0)) {  // shrink the shift of a row that started infeasible, keeping s >= s/2
+              const T shn = tmax(T(0), sh[sl][r] - T(0.5) * sn);
+              sn -= sh[sl][r] - shn;
+              sh[sl][r] = shn;
+            }
+            T ln = lr + adu * dlr;
+            ln = tmin(tmax(ln, mu / (T(opt.kappa) * sn)), T(1e10) * mu / sn);
+            s[sl][r] = sn;
+            lam[sl][r] = ln;
+          }
+          RMPC_UNROLL
+          for (int i = 0; i < NV; ++i) S.st[k].z[i] += alpha * dz[sl][i];
+        }
+      }
+      g.sync();
+    }
+    if (z_out)
+      for (int e = g.lane; e < N * NV; e += G) z_out[e] = S.st[e / NV].z[e % NV];
+    info.iters = it > opt.max_iter ? opt.max_iter : it;
+    info.obj = double(so.f);
+    info.res_stat = double(so.res_stat);
+    info.res_eq = double(so.res_eq);
+    info.res_ineq = double(so.shift_max);
+    info.res_comp = double(so.comp_max);
+    info.mu = double(mu);
+  }
+};
 
 }  // namespace rmpc

@@ -291,8 +291,8 @@ RMPC_HD void stage_values(const T* z, const T* p, StageVal<M, T>& out) {
 
 // rho[r]   : coefficient of g_r g_r' for geometric row r (barrier lambda/s), CA rank-1 is added inside
 // kappa[r] : coefficient of the row's own Hessian (-lambda_r); CA adds -N w / h^2.  Used only if EXACT.
-template <class M, class T, bool EXACT>
-RMPC_HD void stage_derivatives(const T* z, const T* p, const T* rho, const T* kappa, StageDer<M, T>& out) {
+template <class M, class T>
+RMPC_HD void stage_derivatives(const T* z, const T* p, const T* rho, const T* kappa, const bool EXACT, StageDer<M, T>& out) {
   Kin<M, T> kn;
   kin_points<M, T, true>(z, kn);
   RMPC_UNROLL
@@ -482,32 +482,62 @@ RMPC_HD void dyn_value(const T* z, T* xn) {
   }
 }
 
-// AB is the NX x NVAR Jacobian [A B] (row-major).  If EXACT, nu (NX, multiplier of x+ = Phi) weights the
-// second derivative, added into Q (NVAR x NVAR row-major, both triangles).
-template <class M, class T, bool EXACT>
-RMPC_HD void dyn_derivatives(const T* z, T* xn, T* AB, const T* nu, T* Q) {
+// Sparse structure of the Jacobian [A B] (NX x NVAR), column by column, resolved at compile time when the column
+// index is a constant: column j holds n(j) entries (row, value); a value is either a model constant or one of the
+// NVR*NVC z-dependent entries `ABv` (diff-drive: rows 0,1 = d(X+,Y+)/d(th, om, u1, v, u0), i.e. variables
+// VC = {2, 7, 9, 6, 8}, ABv[r*5 + c]).
+template <class M>
+struct DynS {
+  static constexpr int NVR = (M::BASE == 0) ? 0 : 2;
+  static constexpr int NVC = (M::BASE == 0) ? 0 : 5;
+  static constexpr int NABV = NVR * NVC > 0 ? NVR * NVC : 1;
+  static constexpr RMPC_HD int vc(int c) { return c == 0 ? 2 : c == 1 ? 7 : c == 2 ? 9 : c == 3 ? 6 : 8; }
+  // tables as arithmetic on packed literals (a constexpr local array would be rebuilt on the stack at run time)
+  static constexpr RMPC_HD unsigned sel10(int j, unsigned v0, unsigned v1, unsigned v2, unsigned v3, unsigned v4, unsigned v5,
+                                          unsigned v6, unsigned v7, unsigned v8, unsigned v9) {
+    return j == 0 ? v0 : j == 1 ? v1 : j == 2 ? v2 : j == 3 ? v3 : j == 4 ? v4 : j == 5 ? v5 : j == 6 ? v6 : j == 7 ? v7 : j == 8 ? v8 : v9;
+  }
+  static constexpr RMPC_HD int n(int j) {
+    if (M::BASE == 0) return j < M::NQ ? 1 : 2;
+    return int(sel10(j, 1, 1, 3, 1, 1, 1, 3, 4, 3, 4));
+  }
+  static constexpr RMPC_HD int row(int j, int e) {  // one nibble per entry
+    if (M::BASE == 0) return j < M::NQ ? j : (j < M::NX ? (e == 0 ? j - M::NQ : j) : (e == 0 ? j - M::NX : j - M::NX + M::NQ));
+    return int((sel10(j, 0x0000, 0x0001, 0x0210, 0x0003, 0x0004, 0x0005, 0x0610, 0x7210, 0x0610, 0x7210) >> (4 * e)) & 15u);
+  }
+  static constexpr RMPC_HD int var(int j, int e) {  // index into ABv, -1 for a constant entry (nibble 15)
+    if (M::BASE == 0) return -1;
+    const unsigned v = (sel10(j, 0xffff, 0xffff, 0xff50, 0xffff, 0xffff, 0xffff, 0xff83, 0xff61, 0xff94, 0xff72) >> (4 * e)) & 15u;
+    return v == 15u ? -1 : int(v);
+  }
+  static constexpr RMPC_HD double cval(int j, int e) {
+    constexpr double dt = M::DT, h2 = 0.5 * M::DT * M::DT;
+    if (M::BASE == 0) return j < M::NQ ? 1.0 : (j < M::NX ? (e == 0 ? dt : 1.0) : (e == 0 ? h2 : dt));
+    // code per entry: 0 -> 0, 1 -> 1, 2 -> dt, 3 -> dt^2/2
+    const unsigned c = (sel10(j, 0x0001, 0x0001, 0x0100, 0x0001, 0x0001, 0x0001, 0x0100, 0x1200, 0x0200, 0x2300) >> (4 * e)) & 15u;
+    return c == 0u ? 0.0 : c == 1u ? 1.0 : c == 2u ? dt : h2;
+  }
+  template <class T>
+  static RMPC_HD T val(int j, int e, const T* ABv) { return var(j, e) < 0 ? T(cval(j, e)) : ABv[var(j, e) < 0 ? 0 : var(j, e)]; }
+};
+
+// x+ = Phi(z) and the z-dependent Jacobian entries ABv (see DynS).  If `exact`, Hc (5x5 over VC, diff-drive only)
+// receives nu0 * d2(X+) + nu1 * d2(Y+), the multiplier-weighted second derivative of the dynamics.
+template <class M, class T>
+RMPC_HD void dyn_eval(const T* z, T* xn, T* ABv, const bool exact, const T nu0, const T nu1, T Hc[5][5]) {
   const T dt = T(M::DT);
-  RMPC_UNROLL
-  for (int i = 0; i < M::NX * M::NVAR; ++i) AB[i] = T(0);
   if (M::BASE == 0) {
     RMPC_UNROLL
     for (int i = 0; i < M::NQ; ++i) {
       xn[i] = z[i] + dt * z[M::NQ + i] + T(0.5) * dt * dt * z[M::NX + i];
       xn[M::NQ + i] = z[M::NQ + i] + dt * z[M::NX + i];
-      AB[i * M::NVAR + i] = T(1);
-      AB[i * M::NVAR + M::NQ + i] = dt;
-      AB[i * M::NVAR + M::NX + i] = T(0.5) * dt * dt;
-      AB[(M::NQ + i) * M::NVAR + M::NQ + i] = T(1);
-      AB[(M::NQ + i) * M::NVAR + M::NX + i] = dt;
     }
   } else {
     const T h = dt / T(5);
     const T th = z[2], v = z[6], om = z[7], u0 = z[8], u1 = z[9];
     T dx = T(0), dy = T(0);
-    // first derivatives of (dx,dy) w.r.t. [th, om, u1 | v, u0]
     T gx[5] = {0, 0, 0, 0, 0}, gy[5] = {0, 0, 0, 0, 0};
-    T Hc[5][5];
-    if (EXACT) {
+    if (exact) {
       RMPC_UNROLL
       for (int i = 0; i < 5; ++i)
         RMPC_UNROLL
@@ -527,9 +557,9 @@ RMPC_HD void dyn_derivatives(const T* z, T* xn, T* AB, const T* nu, T* Q) {
       for (int i = 0; i < 3; ++i) { gx[i] += -h * s * w * gp[i]; gy[i] += h * c * w * gp[i]; }
       RMPC_UNROLL
       for (int i = 0; i < 2; ++i) { gx[3 + i] += h * c * gw[i]; gy[3 + i] += h * s * gw[i]; }
-      if (EXACT) {
-        const T cpp = h * w * (-nu[0] * c - nu[1] * s);  // d2/dphi2
-        const T cpw = h * (-nu[0] * s + nu[1] * c);      // d2/dphi dw
+      if (exact) {
+        const T cpp = h * w * (-nu0 * c - nu1 * s);  // d2/dphi2
+        const T cpw = h * (-nu0 * s + nu1 * c);      // d2/dphi dw
         RMPC_UNROLL
         for (int i = 0; i < 3; ++i) {
           RMPC_UNROLL
@@ -542,74 +572,19 @@ RMPC_HD void dyn_derivatives(const T* z, T* xn, T* AB, const T* nu, T* Q) {
     xn[0] = z[0] + dx; xn[1] = z[1] + dy; xn[2] = th + dt * om + T(0.5) * dt * dt * u1;
     xn[3] = z[3]; xn[4] = z[4]; xn[5] = z[5];
     xn[6] = v + dt * u0; xn[7] = om + dt * u1;
-    const int vi[5] = {2, 7, 9, 6, 8};
-    AB[0 * M::NVAR + 0] = T(1); AB[1 * M::NVAR + 1] = T(1);
     RMPC_UNROLL
-    for (int i = 0; i < 5; ++i) { AB[0 * M::NVAR + vi[i]] += gx[i]; AB[1 * M::NVAR + vi[i]] += gy[i]; }
-    AB[2 * M::NVAR + 2] = T(1); AB[2 * M::NVAR + 7] = dt; AB[2 * M::NVAR + 9] = T(0.5) * dt * dt;
-    AB[3 * M::NVAR + 3] = T(1); AB[4 * M::NVAR + 4] = T(1); AB[5 * M::NVAR + 5] = T(1);
-    AB[6 * M::NVAR + 6] = T(1); AB[6 * M::NVAR + 8] = dt;
-    AB[7 * M::NVAR + 7] = T(1); AB[7 * M::NVAR + 9] = dt;
-    if (EXACT) {
-      RMPC_UNROLL
-      for (int i = 0; i < 5; ++i)
-        RMPC_UNROLL
-        for (int l = 0; l < 5; ++l) Q[vi[i] * M::NVAR + vi[l]] += Hc[i][l];
-    }
+    for (int i = 0; i < 5; ++i) { ABv[i] = gx[i]; ABv[5 + i] = gy[i]; }
   }
 }
 
-// Entry (i,j) of the Jacobian [A B] for the rows that do not depend on z (all rows for the double integrator,
-// rows 2..7 for the diff-drive model, whose rows 0,1 carry the cos/sin sums).
+// Dense [A B] (row-major NX x NVAR) from the sparse description — tests and debugging only.
 template <class M, class T>
-RMPC_HD T dyn_const_entry(int i, int j) {
-  const T dt = T(M::DT);
-  if (M::BASE == 0) {
-    if (i < M::NQ) {
-      if (j == i) return T(1);
-      if (j == M::NQ + i) return dt;
-      if (j == M::NX + i) return T(0.5) * dt * dt;
-      return T(0);
-    }
-    if (j == i) return T(1);
-    if (j == M::NX + (i - M::NQ)) return dt;
-    return T(0);
-  }
-  if (j == i) return T(1);
-  if (i == 2) return j == 7 ? dt : (j == 9 ? T(0.5) * dt * dt : T(0));
-  if (i == 6) return j == 8 ? dt : T(0);
-  if (i == 7) return j == 9 ? dt : T(0);
-  return T(0);
-}
-template <class M> struct DynRows { static constexpr int NVR = (M::BASE == 0) ? 0 : 2; };  // z-dependent rows of [A B]
-
-// diff-drive only: nu-weighted second derivative of Phi over the variables (th, om, u1, v, u0) = z[2,7,9,6,8]
-template <class M, class T>
-RMPC_HD void dyn_curvature(const T* z, const T* nu, T Hc[5][5]) {
-  const T h = T(M::DT) / T(5);
-  const T th = z[2], v = z[6], om = z[7], u0 = z[8], u1 = z[9];
+RMPC_HD void dyn_dense(const T* ABv, T* AB) {
+  for (int i = 0; i < M::NX * M::NVAR; ++i) AB[i] = T(0);
   RMPC_UNROLL
-  for (int i = 0; i < 5; ++i)
+  for (int j = 0; j < M::NVAR; ++j)
     RMPC_UNROLL
-    for (int j = 0; j < 5; ++j) Hc[i][j] = T(0);
-  RMPC_UNROLL
-  for (int j = 0; j < 5; ++j) {
-    const T a = (T(j) + T(0.5)) * h, b = T(0.5) * T(j) * (T(j) + T(1)) * h * h;
-    T s, c;
-    tsincos(th + a * om + b * u1, &s, &c);
-    const T w = v + a * u0;
-    const T gp[3] = {T(1), a, b};
-    const T gw[2] = {T(1), a};
-    const T cpp = h * w * (-nu[0] * c - nu[1] * s);
-    const T cpw = h * (-nu[0] * s + nu[1] * c);
-    RMPC_UNROLL
-    for (int i = 0; i < 3; ++i) {
-      RMPC_UNROLL
-      for (int l = 0; l < 3; ++l) Hc[i][l] += cpp * gp[i] * gp[l];
-      RMPC_UNROLL
-      for (int l = 0; l < 2; ++l) { Hc[i][3 + l] += cpw * gp[i] * gw[l]; Hc[3 + l][i] += cpw * gp[i] * gw[l]; }
-    }
-  }
+    for (int e = 0; e < DynS<M>::n(j); ++e) AB[DynS<M>::row(j, e) * M::NVAR + j] = DynS<M>::template val<T>(j, e, ABv);
 }
 
 }  // namespace rmpc

