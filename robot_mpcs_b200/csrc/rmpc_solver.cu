@@ -57,7 +57,10 @@ struct rmpc_solver {
 using Shared = ProblemShared<M, double>;
 constexpr size_t kSharedPerWarp = (sizeof(Shared) + 15) / 16 * 16;
 
-__global__ void __launch_bounds__(32 * RMPC_WARPS)
+#ifndef RMPC_MIN_BLOCKS
+#define RMPC_MIN_BLOCKS 1   // resident blocks per SM the register allocation must allow
+#endif
+__global__ void __launch_bounds__(32 * RMPC_WARPS, RMPC_MIN_BLOCKS)
 solve_kernel(int B, const double* __restrict__ xinit, const double* __restrict__ x0, const double* __restrict__ params,
              double* __restrict__ z_out, double* __restrict__ action, rmpc_info info, Options opt, int control_mode,
              int* __restrict__ counter) {
