@@ -16,7 +16,8 @@
  * Plain pointers and sizes only; no torch types.  All functions return 0 on success, negative on API error
  * (message via rmpc_last_error()).  Per-problem solver status is reported only through info.exitflag[]
  * with the FORCESPRO sign convention the reference tests (mpcPlanner.py:263): 1 optimal, 0 iteration limit,
- * <0 failure (-5 factorisation, -6 NaN/Inf, -7 line search).
+ * <0 failure (-5 factorisation, -6 NaN/Inf, -7 no progress / locally infeasible, -8 initial guess on the wrong side
+ * of a ConstraintAvoidance pole).
  */
 #ifndef RMPC_H
 #define RMPC_H
@@ -35,7 +36,7 @@ typedef struct {
 typedef struct {
   int max_iter;     /* iteration cap, default 200 (FORCESPRO default) */
   int hessian;      /* 0 Gauss-Newton, 1 exact Lagrangian Hessian with Gauss-Newton fallback */
-  int precision;    /* 0: float64 throughout; 1: float64 iterates/residuals + float32 Riccati while mu is large */
+  int precision;    /* 0: float64 throughout (the only mode of this build; any other value is rejected by rmpc_solve_batch) */
   int control_mode; /* 0 "acc": action = u of stage 1; 1 "vel": action = z_2[nvar-2nu : nvar-nu] (mpcPlanner.py:275-278) */
   double tol_stat, tol_eq, tol_ineq, tol_comp;
   double mu0, mu_min, reg;
@@ -66,7 +67,7 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* out);
 
 /* Solve B problems.  All array arguments are DEVICE pointers owned by the caller; the call is asynchronous
  * on `stream` (a cudaStream_t passed as void*, NULL = default stream).  z_out / action_out / info may be NULL.
- * Launches: 1 pack kernel, 1 solve kernel, 1 unpack kernel. */
+ * One kernel launch (one warp per problem, persistent grid with a device work queue) after a 4-byte memset. */
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
                      double* z_out, double* action_out, const rmpc_info* info, void* stream);
 

@@ -1,0 +1,45 @@
+"""The C-ABI library of every generated solver directory loads on a CPU-only box and exports every symbol that
+include/rmpc.h declares (no compute calls here: there is no CPU fallback to call)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT, SOLVERS
+
+
+def _declared():
+    hdr = open(os.path.join(ROOT, "include", "rmpc.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(rmpc_[a-z_]+)\s*\(", hdr)))
+
+
+def test_header_declares_the_abi():
+    names = _declared()
+    for n in ("rmpc_create", "rmpc_destroy", "rmpc_solve_batch", "rmpc_solve_batch_host", "rmpc_shift_horizon",
+              "rmpc_set_params", "rmpc_last_error", "rmpc_get_dims", "rmpc_launch_count"):
+        assert n in names
+
+
+def test_every_solver_exports_every_symbol(built):
+    from robot_mpcs_b200.planner.solver import EXPORTS, RmpcDims, load_library
+    dirs = [d for d in sorted(os.listdir(SOLVERS)) if os.path.isdir(os.path.join(SOLVERS, d))]
+    assert len(dirs) >= 5
+    for d in dirs:
+        lib = load_library(os.path.join(SOLVERS, d))
+        for sym in _declared():
+            assert hasattr(lib, sym), (d, sym)
+        assert set(EXPORTS) == set(_declared())
+        dims = RmpcDims()
+        assert lib.rmpc_get_dims(ctypes.byref(dims)) == 0 and dims.nvar == dims.nx + dims.nu
+        assert lib.rmpc_model_name().decode() == d
+
+
+def test_no_gpu_fails_loudly(built):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA device present")
+    from robot_mpcs_b200.planner.solver import Solver, SolverError
+    with pytest.raises(SolverError, match="no CPU fallback|no usable CUDA"):
+        Solver.from_directory(os.path.join(SOLVERS, "pointRobot_n3_005_H20_noSlack"), device=0, max_batch=1)
