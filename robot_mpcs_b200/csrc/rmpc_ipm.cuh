@@ -70,24 +70,23 @@ template <> struct Group<1> {
   RMPC_HD bool any(bool p) const { return p; }
 };
 #if defined(__CUDACC__)
+// double reductions out of line: ~20 call sites x 15 instructions otherwise
+__device__ __noinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __noinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { const double w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
+  return v;
+}
 template <> struct Group<32> {
   int lane;
   __device__ __forceinline__ void sync() const { __syncwarp(); }
-  template <class T> __device__ __forceinline__ T sum(T v) const {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-  }
-  template <class T> __device__ __forceinline__ T max(T v) const {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { const T w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
-    return v;
-  }
-  template <class T> __device__ __forceinline__ T min(T v) const {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { const T w = __shfl_xor_sync(0xffffffffu, v, o); v = w < v ? w : v; }
-    return v;
-  }
+  __device__ __forceinline__ double sum(double v) const { return warp_sum(v); }
+  __device__ __forceinline__ double max(double v) const { return warp_max(v); }
+  __device__ __forceinline__ double min(double v) const { return -warp_max(-v); }
   __device__ __forceinline__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
 };
 #endif
@@ -169,7 +168,8 @@ struct Ipm {
 
   // ---- A: stage-parallel derivatives ----------------------------------------------------------
   RMPC_HD void derivs(const bool exact, const T reg, Red<T>& o) {
-    T f = T(0), theta = T(0), logs = T(0), res_eq = T(0), cmin = T(1e300), cmax = T(0), msum = T(0), shmax = T(0), smin = T(1e300);
+    LogAcc<T> lacc;
+    T f = T(0), theta = T(0), res_eq = T(0), cmin = T(1e300), cmax = T(0), msum = T(0), shmax = T(0), smin = T(1e300);
     bool pole = false;
     RMPC_UNROLL
     for (int sl = 0; sl < SLOTS; ++sl) {
@@ -186,9 +186,9 @@ struct Ipm {
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
           const T sr = s[sl][r], lr = lam[sl][r];
-          y1[r] = T(1) / sr;
+          y1[r] = trcp(sr);
           sig[r] = lr * y1[r];
-          logs += tlog(sr);
+          lacc.mul(sr);
           cmax = tmax(cmax, sr * lr);
           cmin = tmin(cmin, sr * lr);
           msum += lr;
@@ -255,7 +255,7 @@ struct Ipm {
         for (int i = 0; i < Dims<M>::NQD; ++i) st.Qd[i] = Qd[i];
       }
     }
-    o.f = g.sum(f); o.theta = g.sum(theta); o.logs = g.sum(logs); o.res_eq = g.max(res_eq);
+    o.f = g.sum(f); o.theta = g.sum(theta); o.logs = g.sum(lacc.value()); o.res_eq = g.max(res_eq);
     o.comp_min = g.min(cmin); o.comp_max = g.max(cmax); o.mult_sum = g.sum(msum); o.shift_max = g.max(shmax); o.s_min = g.min(smin);
     o.pole = g.any(pole);
     g.sync();
@@ -325,7 +325,7 @@ struct Ipm {
           RMPC_UNROLL
           for (int c = 0; c < j; ++c) dd -= L[j * NU + c] * L[j * NU + c];
           if (!(dd > T(0))) { ok = false; dd = T(1); }
-          const T il = T(1) / tsqrt(dd);
+          const T il = trsqrt(dd);
           L[j * NU + j] = il;  // reciprocal pivot
           RMPC_UNROLL
           for (int i = j + 1; i < NU; ++i) {
@@ -514,7 +514,7 @@ struct Ipm {
       // ---- Newton step, linear step-length estimates, merit slope
       rollout(mu);
       const T tau = tmax(T(opt.tau_min), T(1) - mu);
-      T ap = T(1), ad = T(1), dphi = T(0);
+      T rp = T(0), rd = T(0), dphi = T(0);
       RMPC_UNROLL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
@@ -527,14 +527,16 @@ struct Ipm {
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];
             const T dsr = gd[r];
-            const T dlr = mu / sr - lr - (lr / sr) * dsr;
-            if (dsr < T(0)) ap = tmin(ap, -tau * sr / dsr);
-            if (dlr < T(0)) ad = tmin(ad, -tau * lr / dlr);
-            dphi -= mu * dsr / sr;
+            const T rs = trcp(sr);
+            const T dlr = mu * rs - lr - (lr * rs) * dsr;
+            rp = tmax(rp, -dsr * rs);            // largest relative decrease of a slack ...
+            rd = tmax(rd, -dlr * trcp(lr));      // ... and of a multiplier, for the fraction-to-boundary rule
+            dphi -= mu * dsr * rs;
           }
         }
       }
-      ap = g.min(ap); ad = g.min(ad); dphi = g.sum(dphi);
+      rp = g.max(rp); rd = g.max(rd); dphi = g.sum(dphi);
+      const T ap = rp > tau ? tau / rp : T(1), ad = rd > tau ? tau / rd : T(1);
       if (so.theta > T(1e-14)) {
         const T need = dphi / (T(0.9) * so.theta);
         if (need > rho_pen) rho_pen = need * T(1.1) + T(1e-3);
@@ -546,7 +548,8 @@ struct Ipm {
       bool accepted = false;
       int nls = 0;
       for (int ls = 0; ls < 30; ++ls) {
-        T f = T(0), theta = T(0), logs = T(0);
+        T f = T(0), theta = T(0);
+        LogAcc<T> la;
         bool bad = false;
         RMPC_UNROLL
         for (int sl = 0; sl < SLOTS; ++sl) {
@@ -571,7 +574,7 @@ struct Ipm {
                 if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(s[sl][r]), double(lam[sl][r]), double(stv), double(s[sl][r] + alpha * gd[r]), double(alpha)); }
 #endif
               }
-              logs += tlog(tmax(stv, T(1e-300)));
+              la.mul(tmax(stv, T(1e-300)));
             }
             if (k < N - 1) {
               T xn[NX];
@@ -581,7 +584,8 @@ struct Ipm {
             }
           }
         }
-        f = g.sum(f); theta = g.sum(theta); logs = g.sum(logs);
+        f = g.sum(f); theta = g.sum(theta);
+        const T logs = g.sum(la.value());
         bad = g.any(bad);
         const T phi = f - mu * logs + rho_pen * theta;
         const T tol_phi = T(10) * T(sizeof(T) == 8 ? 2.2e-16 : 1.2e-7) * tabs(phi0);
@@ -612,7 +616,8 @@ struct Ipm {
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];
-            const T dlr = mu / sr - lr - (lr / sr) * gd[r];
+            const T rs = trcp(sr);
+            const T dlr = mu * rs - lr - (lr * rs) * gd[r];
             T sn = htr[sl][r] + sh[sl][r];
             if (sh[sl][r] > T(0)) {  // shrink the shift of a row that started infeasible, keeping s >= s/2
               const T shn = tmax(T(0), sh[sl][r] - T(0.5) * sn);
@@ -620,7 +625,8 @@ struct Ipm {
               sh[sl][r] = shn;
             }
             T ln = lr + adu * dlr;
-            ln = tmin(tmax(ln, mu / (T(opt.kappa) * sn)), T(1e10) * mu / sn);
+            const T mus = mu * trcp(sn);
+            ln = tmin(tmax(ln, mus / T(opt.kappa)), T(1e10) * mus);
             s[sl][r] = sn;
             lam[sl][r] = ln;
           }

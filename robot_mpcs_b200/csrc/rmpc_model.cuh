@@ -35,10 +35,64 @@ template <class T> RMPC_HD T tmin(T a, T b) { return a < b ? a : b; }
 template <class T> RMPC_HD T tabs(T a) { return a < T(0) ? -a : a; }
 RMPC_HD float tsqrt(float a) { return sqrtf(a); }
 RMPC_HD double tsqrt(double a) { return sqrt(a); }
-RMPC_HD void tsincos(float a, float* s, float* c) { *s = sinf(a); *c = cosf(a); }
-RMPC_HD void tsincos(double a, double* s, double* c) { *s = sin(a); *c = cos(a); }
 RMPC_HD float tlog(float a) { return logf(a); }
+RMPC_HD float trcp(float a) { return 1.0f / a; }
+RMPC_HD float trsqrt(float a) { return 1.0f / sqrtf(a); }
+RMPC_HD void tsincos(float a, float* s, float* c) { *s = sinf(a); *c = cosf(a); }
+#if defined(__CUDA_ARCH__)
+// Device: the libm expansions of sincos / log are ~150 / ~60 instructions each; one out-of-line copy keeps the solve
+// kernel inside the instruction cache.  Reciprocal and reciprocal square root: float seed + Newton steps in double
+// (full double accuracy to a few ulp for the magnitudes met here, 1e-30 .. 1e30), instead of the IEEE division /
+// square-root sequences with their slow-path branches.
+__device__ __noinline__ void tsincos(double a, double* s, double* c) { sincos(a, s, c); }
+__device__ __noinline__ double tlog(double a) { return log(a); }
+__device__ __forceinline__ double trcp(double a) {
+  double r = double(__frcp_rn(float(a)));
+  r = r * (2.0 - a * r);
+  r = r * (2.0 - a * r);
+  return r;
+}
+__device__ __forceinline__ double trsqrt(double a) {
+  double r = double(rsqrtf(float(a)));
+  r = r * (1.5 - 0.5 * a * r * r);
+  r = r * (1.5 - 0.5 * a * r * r);
+  r = r * (1.5 - 0.5 * a * r * r);
+  return r;
+}
+#else
+RMPC_HD void tsincos(double a, double* s, double* c) { *s = sin(a); *c = cos(a); }
 RMPC_HD double tlog(double a) { return log(a); }
+RMPC_HD double trcp(double a) { return 1.0 / a; }
+RMPC_HD double trsqrt(double a) { return 1.0 / sqrt(a); }
+#endif
+
+// sum_i log(x_i) as log(prod mantissas) + ln2 * sum exponents: one log per stage instead of one per row.
+template <class T> struct LogAcc;
+template <> struct LogAcc<double> {
+  double m;
+  int e;
+  RMPC_HD LogAcc() : m(1.0), e(0) {}
+  RMPC_HD void mul(double x) {  // x > 0, normal
+#if defined(__CUDA_ARCH__)
+    const long long b = __double_as_longlong(x);
+    e += int((b >> 52) & 0x7ff) - 1022;
+    m *= __longlong_as_double((b & 0x800fffffffffffffLL) | 0x3fe0000000000000LL);
+#else
+    int ex;
+    m *= frexp(x, &ex);
+    e += ex;
+#endif
+    if (m < 1e-200) { m *= 1e200; lg += -460.51701859880916; }  // ln(1e-200): keeps long products normal
+  }
+  double lg = 0.0;
+  RMPC_HD double value() const { return tlog(m) + 0.6931471805599453 * double(e) + lg; }
+};
+template <> struct LogAcc<float> {
+  float a;
+  RMPC_HD LogAcc() : a(0.0f) {}
+  RMPC_HD void mul(float x) { a += logf(x); }
+  RMPC_HD float value() const { return a; }
+};
 
 // ------------------------------------------------------------------------------------------------
 // Kinematics: world frames of the NJ tree joints that matter, positions of the NPT points of interest
@@ -227,24 +281,24 @@ RMPC_HD T geo_value(const Kin<M, T>& kn, const T* p, int r, T* nvec, T* dist_out
   if (typ == GEO_SPHERE) {
     const int o = M::geo_p(r);
     T d[3] = {kn.p[A][0] - p[o], kn.p[A][1] - p[o + 1], kn.p[A][2] - p[o + 2]};
-    const T dist = tsqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-    const T inv = T(1) / tmax(dist, T(1e-12));
+    const T d2 = tmax(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], T(1e-24));
+    const T inv = trsqrt(d2), dist = d2 * inv;
     nvec[0] = d[0] * inv; nvec[1] = d[1] * inv; nvec[2] = d[2] * inv;
     *dist_out = dist;
     return dist - p[o + 3] - rb;
   } else if (typ == GEO_PLANE) {
     const int o = M::geo_p(r);
     const T v = p[o] * kn.p[A][0] + p[o + 1] * kn.p[A][1] + p[o + 2] * kn.p[A][2] + p[o + 3];
-    const T nrm = tsqrt(p[o] * p[o] + p[o + 1] * p[o + 1] + p[o + 2] * p[o + 2]);
-    const T sg = (v < T(0) ? T(-1) : T(1)) / nrm;
+    const T inrm = trsqrt(p[o] * p[o] + p[o + 1] * p[o + 1] + p[o + 2] * p[o + 2]);
+    const T sg = v < T(0) ? -inrm : inrm;
     nvec[0] = sg * p[o]; nvec[1] = sg * p[o + 1]; nvec[2] = sg * p[o + 2];
     *dist_out = T(0);
-    return tabs(v) / nrm - rb;
+    return tabs(v) * inrm - rb;
   } else {
     const int Bp = M::geo_b(r);
     T d[3] = {kn.p[A][0] - kn.p[Bp][0], kn.p[A][1] - kn.p[Bp][1], kn.p[A][2] - kn.p[Bp][2]};
-    const T dist = tsqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-    const T inv = T(1) / tmax(dist, T(1e-12));
+    const T d2 = tmax(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], T(1e-24));
+    const T inv = trsqrt(d2), dist = d2 * inv;
     nvec[0] = d[0] * inv; nvec[1] = d[1] * inv; nvec[2] = d[2] * inv;
     *dist_out = dist;
     return dist - T(2) * rb;
@@ -280,7 +334,7 @@ RMPC_HD void stage_values(const T* z, const T* p, StageVal<M, T>& out) {
     const T hv = out.h[M::ca_row(i)];
     if (w != T(0)) {
       if (hv <= T(0)) pole = true;
-      f += T(M::N) * w / hv;
+      f += T(M::N) * w * trcp(hv);
     }
   }
   RMPC_UNROLL
@@ -362,7 +416,7 @@ RMPC_HD void stage_derivatives(const T* z, const T* p, const T* rho, const T* ka
     const int row = M::ca_row(i);
     const T hv = out.h[row];
     if (hv <= T(0)) pole = true;
-    const T ih = T(1) / hv;
+    const T ih = trcp(hv);
     const T c0 = T(M::N) * w * ih;   // value
     const T c1 = -c0 * ih;           // d/dh
     const T c2 = T(2) * c0 * ih * ih;  // d2/dh2
@@ -384,7 +438,7 @@ RMPC_HD void stage_derivatives(const T* z, const T* p, const T* rho, const T* ka
   for (int r = 0; r < M::NGEO; ++r) {
     T c = r1[r];
     if (EXACT && M::geo_type(r) != GEO_PLANE) {
-      const T kd = kap[r] / tmax(dist[r], T(1e-12));
+      const T kd = kap[r] * trcp(tmax(dist[r], T(1e-12)));
       c -= kd;  // kappa (I - n n')/dist  ->  -kappa/dist g g'  + kappa/dist J'J
       if (M::geo_type(r) == GEO_SPHERE) {
         cJJ[M::geo_a(r)] += kd;
