@@ -139,6 +139,30 @@ def cpu_baseline(workload, B_sample, seed, threads=0):
                       f"mean iters {float(r['iters'].mean()):.1f}"}, dt, conv
 
 
+def single_solve_latency(workload, n, solve_one):
+    """p50/p99 wall time of `n` single solves (B = 1) on `n` different scenarios of the workload; solve_one(xinit, x0, params)
+    takes host arrays and returns once the action is back on the host (BASELINE.json metric, second half)."""
+    s = make_inputs(workload, n, seed=4242)
+    xs, x0s, ps = (np.ascontiguousarray(s[k]) for k in ("xinit", "x0", "params"))
+    for i in range(min(n, 10)):
+        solve_one(xs[i:i + 1], x0s[i:i + 1], ps[i:i + 1])
+    ts, conv = [], 0
+    for i in range(n):
+        t = time.perf_counter()
+        ef = solve_one(xs[i:i + 1], x0s[i:i + 1], ps[i:i + 1])
+        ts.append(time.perf_counter() - t)
+        conv += int(ef == 1)
+    ts = np.array(ts) * 1e3
+    return {"unit": "ms", "p50": float(np.percentile(ts, 50)), "p99": float(np.percentile(ts, 99)), "mean": float(ts.mean()),
+            "n": n, "converged": conv}
+
+
+def cpu_single_solve_latency(workload, n):
+    from oracle.build_twin import Twin
+    tw = Twin(os.path.join(SOLVERS, WORKLOADS[workload][0]))
+    return single_solve_latency(workload, n, lambda x, x0, p: int(tw.solve(x, x0, p, nthreads=1)["exitflag"][0]))
+
+
 # ------------------------------------------------------------------------------------------------
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -160,6 +184,8 @@ def run_reference(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "batch_per_step": Bs, "note": "CPU twin (port) of the same IPM/Riccati; FORCESPRO/IPOPT unavailable on this box"},
             "cpu_baseline": base, "e2e": {"value": val, "unit": "converged solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if args.latency_samples > 0:
+        line["single_solve_latency"] = dict(cpu_single_solve_latency(args.workload, args.latency_samples), path="CPU twin, 1 thread, B=1")
     print(json.dumps(line), flush=True)
 
 
@@ -277,6 +303,13 @@ def run_ours(args):
     h2d = 8 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar)
     d2h = 8 * B * (solver.nu + 5) + 4 * B * 2
 
+    lat = None
+    if rank == 0 and args.latency_samples > 0:
+        def one(x, x0, p):
+            return int(solver.solve_batch(x, x0, p, want_z=False, want_info=True)["exitflag"][0])
+        lat = dict(single_solve_latency(args.workload, args.latency_samples, one),
+                   path="rmpc_solve_batch_host, B=1: H2D of xinit/x0/params + one-warp solve + D2H of action/info, wall clock")
+
     if rank == 0:
         peaks = {}
         try:
@@ -312,6 +345,10 @@ def run_ours(args):
         }
         if base is not None:
             line["cpu_baseline"] = base
+        if lat is not None:
+            line["single_solve_latency"] = lat
+            if world == 1 and not args.no_cpu_baseline:
+                line["cpu_baseline"]["single_solve_latency"] = cpu_single_solve_latency(args.workload, args.latency_samples)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -329,6 +366,7 @@ def main():
     ap.add_argument("--hessian", type=int, default=1)
     ap.add_argument("--ref-sample", type=int, default=4096, help="scenarios per CPU-baseline pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--latency-samples", type=int, default=300, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

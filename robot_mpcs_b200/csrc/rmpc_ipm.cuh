@@ -68,6 +68,7 @@ template <> struct Group<1> {
   template <class T> RMPC_HD T max(T v) const { return v; }
   template <class T> RMPC_HD T min(T v) const { return v; }
   RMPC_HD bool any(bool p) const { return p; }
+  template <class T> RMPC_HD T bcast(T v, int) const { return v; }
 };
 #if defined(__CUDACC__)
 // double reductions out of line: ~20 call sites x 15 instructions otherwise
@@ -88,6 +89,7 @@ template <> struct Group<32> {
   __device__ __forceinline__ double max(double v) const { return warp_max(v); }
   __device__ __forceinline__ double min(double v) const { return -warp_max(-v); }
   __device__ __forceinline__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
+  __device__ __forceinline__ double bcast(double v, int src) const { return __shfl_sync(0xffffffffu, v, src); }
 };
 #endif
 
@@ -111,30 +113,44 @@ RMPC_HD void load_params(const ParamView<T>& pv, int k, T* p) {
 template <class M> struct Dims {
   static constexpr int NDS = (M::BASE == 0) ? M::NQ : M::NVAR;   // variables coupled by the dense part of the stage Hessian
   static constexpr int NQD = NDS * (NDS + 1) / 2;
+  static constexpr int NHD = M::NVAR - NDS > 0 ? M::NVAR - NDS : 1;  // variables with a diagonal-only Hessian
   static constexpr int NVA = M::NVAR + 3;                         // [A B]-sized blocks carry 3 extra columns: g0, g1, adjoint
+  static constexpr int NKK = M::NU * M::NX + 2 * M::NU;           // feedback gain K and the two feed-forward vectors
+  static constexpr int NPRE = NQD + NHD + 2 * M::NVAR;            // Hessian + g1 + gl: dead once phase 1 of the sweep has read them
+  static constexpr int OFF0 = NPRE > NKK ? NPRE : NKK;            // offset of g0 (live until the line search) in StageShared::Qs
+  static constexpr int OFF1 = OFF0 - 2 * M::NVAR, OFFL = OFF0 - M::NVAR;
+  static constexpr int LDF = (NVA % 2) ? NVA : NVA + 1;           // odd row stride of F / PAB: row- and column-wise accesses are conflict-free
+  // dense Hessian part: packed lower triangle stored column by column, so that the lane that owns column b reads
+  // entry (a, b), a >= b, at qcol(b) + a with a compile-time `a`
+  static constexpr RMPC_HD int qcol(int b) { return b * (NDS - 1) - b * (b - 1) / 2; }
+  static constexpr RMPC_HD int qidx(int a, int b) { return a >= b ? qcol(b) + a : qcol(a) + b; }
 };
 
 template <class M, class T>
 struct StageShared {
   T z[M::NVAR];
-  T qt0[M::NVAR];            // cost gradient
-  T qt1[M::NVAR];            // -G' (1/s): coefficient of mu in the barrier gradient
-  T gl[M::NVAR];             // cost gradient - G' lambda
-  T Qd[Dims<M>::NQD];        // dense symmetric part of the Hessian over the first NDS variables (lower triangle)
-  T Hd[M::NVAR];             // diagonal part
+  T dz[M::NVAR];             // Newton step of this stage (written by the roll-out)
+  // [Qd | Hd | .. | g1 | gl | g0]: dense Hessian part (Dims::qidx), diagonal entries of the variables NDS..NVAR-1,
+  // g1 = -G'(1/s) (coefficient of mu in the barrier gradient), gl = cost gradient - G' lambda, g0 = cost gradient.
+  // Everything before g0 is dead once phase 1 of the sweep has consumed it; K | kff0 | kff1 then reuse that space.
+  T Qs[Dims<M>::OFF0 + M::NVAR];
   T ABv[DynS<M>::NABV];      // z-dependent entries of [A B]
   T d[M::NX];                // Phi(z_k) - x_{k+1}
-  T K[M::NU * M::NX];        // feedback gain
-  T kff0[M::NU], kff1[M::NU];
   T nu01[2];                 // adjoint of (X+, Y+) from the previous sweep (diff-drive curvature)
+  RMPC_HD T g0(int i) const { return Qs[Dims<M>::OFF0 + i]; }
+  RMPC_HD T& K(int l, int c) { return Qs[l * M::NX + c]; }
+  RMPC_HD T K(int l, int c) const { return Qs[l * M::NX + c]; }
+  RMPC_HD T& kff0(int l) { return Qs[M::NU * M::NX + l]; }
+  RMPC_HD T kff0(int l) const { return Qs[M::NU * M::NX + l]; }
+  RMPC_HD T& kff1(int l) { return Qs[M::NU * M::NX + M::NU + l]; }
+  RMPC_HD T kff1(int l) const { return Qs[M::NU * M::NX + M::NU + l]; }
 };
 
 template <class M, class T>
 struct ProblemShared {
   StageShared<M, T> st[M::N];
-  T P[M::NX * M::NX], p0[M::NX], p1[M::NX], nu[M::NX];
-  T PAB[M::NX * Dims<M>::NVA];
-  T F[M::NVAR * Dims<M>::NVA];
+  T PAB[M::NX * Dims<M>::LDF];     // P_{k+1} [A B | d-term | p1 | nu] of the stage being processed
+  T F[M::NVAR * Dims<M>::LDF];     // [Q | g0 | g1 | gl] + [A B]' PAB: lower triangle of the matrix part, Fxx mirrored
 };
 
 template <class T>
@@ -160,11 +176,9 @@ struct Ipm {
   // per-lane state of the stages this lane owns
   T lam[SLOTS][NH], s[SLOTS][NH], sh[SLOTS][NH], htr[SLOTS][NH];
   T Gg[SLOTS][NGEO1][NQ];
-  T dz[SLOTS][NV], dxn[SLOTS][NX];
 
   RMPC_HD Ipm(const Group<G>& g_, ProblemShared<M, T>& S_, const ParamView<T>& pv_, const Options& o_) : g(g_), S(S_), pv(pv_), opt(o_) {}
 
-  static RMPC_HD int tri(int a, int b) { return a >= b ? a * (a + 1) / 2 + b : b * (b + 1) / 2 + a; }
 
   // ---- A: stage-parallel derivatives ----------------------------------------------------------
   RMPC_HD void derivs(const bool exact, const T reg, Red<T>& o) {
@@ -221,16 +235,22 @@ struct Ipm {
           glv[M::lim_var(r)] -= T(M::lim_sign(r)) * lam[sl][M::lim_row(r)];
           sd.Hd[M::lim_var(r)] += sig[M::lim_row(r)];
         }
+        constexpr int NQD = Dims<M>::NQD;
         RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) { st.qt0[i] = sd.g[i]; st.qt1[i] = q1[i]; st.gl[i] = glv[i]; st.Hd[i] = sd.Hd[i] + reg; }
-        // dense part of the Hessian
-        T Qd[Dims<M>::NQD];
+        for (int i = 0; i < NV; ++i) { st.Qs[Dims<M>::OFF0 + i] = sd.g[i]; st.Qs[Dims<M>::OFF1 + i] = q1[i]; st.Qs[Dims<M>::OFFL + i] = glv[i]; }
+        // dense part of the Hessian (lower triangle, Dims::qidx) with the diagonal folded in
+        T Qd[NQD];
         RMPC_UNROLL
-        for (int i = 0; i < Dims<M>::NQD; ++i) Qd[i] = T(0);
+        for (int i = 0; i < NQD; ++i) Qd[i] = T(0);
         RMPC_UNROLL
         for (int a = 0; a < NQ; ++a)
           RMPC_UNROLL
-          for (int b = 0; b <= a; ++b) Qd[a * (a + 1) / 2 + b] = sd.Hqq[a * NQ + b];
+          for (int b = 0; b <= a; ++b) Qd[Dims<M>::qidx(a, b)] = sd.Hqq[a * NQ + b];
+        RMPC_UNROLL
+        for (int i = 0; i < NV; ++i) {
+          if (i < NDS) Qd[Dims<M>::qidx(i, i)] += sd.Hd[i] + reg;
+          else st.Qs[NQD + (i < NDS ? 0 : i - NDS)] = sd.Hd[i] + reg;
+        }
         if (k < N - 1) {
           T xn[NX], ABv[DS::NABV], Hc[5][5];
           dyn_eval<M, T>(zk, xn, ABv, exact, st.nu01[0], st.nu01[1], Hc);
@@ -248,11 +268,11 @@ struct Ipm {
             for (int a = 0; a < 5; ++a)
               RMPC_UNROLL
               for (int b = 0; b < 5; ++b)
-                if (DS::vc(a) >= DS::vc(b)) Qd[DS::vc(a) * (DS::vc(a) + 1) / 2 + DS::vc(b)] += Hc[a][b];
+                if (DS::vc(a) >= DS::vc(b)) Qd[Dims<M>::qidx(DS::vc(a), DS::vc(b))] += Hc[a][b];
           }
         }
         RMPC_UNROLL
-        for (int i = 0; i < Dims<M>::NQD; ++i) st.Qd[i] = Qd[i];
+        for (int i = 0; i < NQD; ++i) st.Qs[i] = Qd[i];
       }
     }
     o.f = g.sum(f); o.theta = g.sum(theta); o.logs = g.sum(lacc.value()); o.res_eq = g.max(res_eq);
@@ -262,63 +282,49 @@ struct Ipm {
   }
 
   // ---- B: backward Riccati sweep, shared by the lanes -------------------------------------------
+  // Three barriers per stage.  P_{k+1} itself is never stored: the lanes that own its rows keep them in registers
+  // just long enough to form PAB for the next (earlier) stage.
   RMPC_HD void sweep(Red<T>& o) {
-    for (int e = g.lane; e < NX * NX; e += G) S.P[e] = T(0);
-    for (int e = g.lane; e < NX; e += G) { S.p0[e] = T(0); S.p1[e] = T(0); S.nu[e] = T(0); }
-    g.sync();
+    constexpr int LDF = Dims<M>::LDF, NQD = Dims<M>::NQD;
     T res_stat = T(0), nsum = T(0);
     bool ok = true;
     for (int k = N - 1; k >= 0; --k) {
       StageShared<M, T>& st = S.st[k];
       const bool dyn = k < N - 1;
-      // phase 1: PAB = P [A B | d-term | p1 | nu]
-      if (dyn) {
-        for (int i = g.lane; i < NX; i += G) {
-          T Pi[NX];
-          RMPC_UNROLL
-          for (int l = 0; l < NX; ++l) Pi[l] = S.P[i * NX + l];
-          RMPC_UNROLL
-          for (int j = 0; j < NV; ++j) {
-            T a = T(0);
-            RMPC_UNROLL
-            for (int e = 0; e < DS::n(j); ++e) a += DS::template val<T>(j, e, st.ABv) * Pi[DS::row(j, e)];
-            S.PAB[i * NVA + j] = a;
-          }
-          T a = S.p0[i];
-          RMPC_UNROLL
-          for (int l = 0; l < NX; ++l) a += Pi[l] * st.d[l];
-          S.PAB[i * NVA + NV] = a;
-          S.PAB[i * NVA + NV + 1] = S.p1[i];
-          S.PAB[i * NVA + NV + 2] = S.nu[i];
-        }
-        g.sync();
-      }
-      // phase 2: F = [Q | qt0 | qt1 | gl] + [A B]' PAB
+      // phase 1: lane j owns column j of F = [Q | g0 | g1 | gl] + [A B]' PAB; of the matrix part only the lower
+      // triangle (i >= j) is meaningful
       for (int j = g.lane; j < NVA; j += G) {
+        const bool rhs = j >= NV;
+        // column j of [Q | g0 | g1 | gl] starts at Qs[qoff]; the loads are unconditional (what they fetch above the
+        // diagonal is never stored)
+        const int qoff = rhs ? (j == NV ? Dims<M>::OFF0 : Dims<M>::OFF0 + (j - NV - 3) * NV) : (j < NDS ? Dims<M>::qcol(j) : 0);
+        T a[NV];
         RMPC_UNROLL
         for (int i = 0; i < NV; ++i) {
-          T a;
-          if (j < NV) {
-            a = (i == j) ? st.Hd[i] : T(0);
-            if (i < NDS && j < NDS) a += st.Qd[tri(i, j)];
-          } else {
-            a = (j == NV) ? st.qt0[i] : (j == NV + 1 ? st.qt1[i] : st.gl[i]);
-          }
-          if (dyn) {
-            RMPC_UNROLL
-            for (int e = 0; e < DS::n(i); ++e) a += DS::template val<T>(i, e, st.ABv) * S.PAB[DS::row(i, e) * NVA + j];
-          }
-          S.F[i * NVA + j] = a;
+          const T q = st.Qs[qoff + i];
+          if (i < NDS) a[i] = q;
+          else { const T h = st.Qs[NQD + (i < NDS ? 0 : i - NDS)]; a[i] = rhs ? q : (j == i ? h : T(0)); }
         }
+        if (dyn) {
+          T w[NX];
+          RMPC_UNROLL
+          for (int l = 0; l < NX; ++l) w[l] = S.PAB[l * LDF + j];
+          RMPC_UNROLL
+          for (int i = 0; i < NV; ++i)
+            RMPC_UNROLL
+            for (int e = 0; e < DS::n(i); ++e) a[i] += DS::template val<T>(i, e, st.ABv) * w[DS::row(i, e)];
+        }
+        RMPC_UNROLL
+        for (int i = 0; i < NV; ++i) S.F[i * LDF + j] = a[i];  // above the diagonal: junk that nobody reads
       }
       g.sync();
-      // phase 3: Cholesky of Fuu (every lane, redundantly) and the NX+2 solves (one column per lane)
+      // phase 2: Cholesky of Fuu (every lane, redundantly) and the NX+2 solves (one column per lane)
       {
         T L[NU * NU];
         RMPC_UNROLL
         for (int a = 0; a < NU; ++a)
           RMPC_UNROLL
-          for (int b = 0; b <= a; ++b) L[a * NU + b] = S.F[(NX + a) * NVA + NX + b];
+          for (int b = 0; b <= a; ++b) L[a * NU + b] = S.F[(NX + a) * LDF + NX + b];
         RMPC_UNROLL
         for (int j = 0; j < NU; ++j) {
           T dd = L[j * NU + j];
@@ -336,13 +342,13 @@ struct Ipm {
           }
         }
         RMPC_UNROLL
-        for (int j = 0; j < NU; ++j) res_stat = tmax(res_stat, tabs(S.F[(NX + j) * NVA + NV + 2]));
+        for (int j = 0; j < NU; ++j) res_stat = tmax(res_stat, tabs(S.F[(NX + j) * LDF + NV + 2]));
         for (int c = g.lane; c < NX + 2; c += G) {
           const int col = c < NX ? c : NV + (c - NX);
           T y[NU];
           RMPC_UNROLL
           for (int i = 0; i < NU; ++i) {
-            T v = S.F[(NX + i) * NVA + col];
+            T v = S.F[(NX + i) * LDF + col];
             RMPC_UNROLL
             for (int l = 0; l < i; ++l) v -= L[i * NU + l] * y[l];
             y[i] = v * L[i * NU + i];
@@ -356,34 +362,46 @@ struct Ipm {
           }
           RMPC_UNROLL
           for (int i = 0; i < NU; ++i) {
-            if (c < NX) st.K[i * NX + c] = -y[i];
-            else if (c == NX) st.kff0[i] = -y[i];
-            else st.kff1[i] = -y[i];
+            st.Qs[c < NX ? i * NX + c : NU * NX + (c - NX) * NU + i] = -y[i];  // K(i, c) | kff0(i) | kff1(i)
           }
         }
       }
       g.sync();
-      // phase 4: P = Fxx + Fux' K, p = fx + Fux' kff, adjoint nu = x-part of the Lagrangian gradient
-      for (int e = g.lane; e < NX * NX + 3 * NX; e += G) {
-        if (e < NX * NX) {
-          const int i = e / NX, j = e - i * NX;
-          T v = S.F[i * NVA + j];
+      // phase 3: lane i owns row i of P = Fxx + Fux' K, p = fx + Fux' kff and the adjoint nu (x-part of the Lagrangian
+      // gradient), and turns them at once into row i of PAB = P [A B | d-term | p1 | nu] of the stage before
+      for (int i = g.lane; i < NX; i += G) {
+        T fu[NU];
+        RMPC_UNROLL
+        for (int l = 0; l < NU; ++l) fu[l] = S.F[(NX + l) * LDF + i];
+        T Pi[NX];
+        RMPC_UNROLL
+        for (int j = 0; j < NX; ++j) {
+          T v = S.F[i >= j ? i * LDF + j : j * LDF + i];  // Fxx from its lower triangle
           RMPC_UNROLL
-          for (int l = 0; l < NU; ++l) v += S.F[(NX + l) * NVA + i] * st.K[l * NX + j];
-          S.P[e] = v;
-        } else {
-          const int t = e - NX * NX, which = t / NX, i = t - which * NX;
-          if (which == 2) {
-            const T v = S.F[i * NVA + NV + 2];
-            S.nu[i] = v;
-            nsum += tabs(v);
-            if (k > 0 && i < 2) S.st[k - 1].nu01[i] = v;
-          } else {
-            T v = S.F[i * NVA + NV + which];
+          for (int l = 0; l < NU; ++l) v += fu[l] * st.K(l, j);
+          Pi[j] = v;
+        }
+        T p0 = S.F[i * LDF + NV], p1 = S.F[i * LDF + NV + 1];
+        const T nui = S.F[i * LDF + NV + 2];
+        RMPC_UNROLL
+        for (int l = 0; l < NU; ++l) { p0 += fu[l] * st.kff0(l); p1 += fu[l] * st.kff1(l); }
+        nsum += tabs(nui);
+        if (k > 0) {
+          StageShared<M, T>& sp = S.st[k - 1];
+          if (i < 2) sp.nu01[i] = nui;
+          RMPC_UNROLL
+          for (int j = 0; j < NV; ++j) {
+            T a = T(0);
             RMPC_UNROLL
-            for (int l = 0; l < NU; ++l) v += S.F[(NX + l) * NVA + i] * (which == 0 ? st.kff0[l] : st.kff1[l]);
-            if (which == 0) S.p0[i] = v; else S.p1[i] = v;
+            for (int e = 0; e < DS::n(j); ++e) a += DS::template val<T>(j, e, sp.ABv) * Pi[DS::row(j, e)];
+            S.PAB[i * LDF + j] = a;
           }
+          T a = p0;
+          RMPC_UNROLL
+          for (int l = 0; l < NX; ++l) a += Pi[l] * sp.d[l];
+          S.PAB[i * LDF + NV] = a;
+          S.PAB[i * LDF + NV + 1] = p1;
+          S.PAB[i * LDF + NV + 2] = nui;
         }
       }
       g.sync();
@@ -394,55 +412,63 @@ struct Ipm {
     o.finite = (o.f == o.f) && (o.res_stat == o.res_stat) && (o.theta == o.theta) && (o.mult_sum == o.mult_sum);
   }
 
-  // ---- C: forward roll-out (every lane runs it, keeps the step of its own stages) -------------------
+  // ---- C: forward roll-out: dz_k = (dx_k, K_k dx_k + kff_k), dx_{k+1} = [A B] dz_k + d_k, into shared memory.
+  // Lane j < NU evaluates row j of the feedback law, the rows are exchanged by shuffles, and every lane carries dx.
   RMPC_HD void rollout(const T mu) {
     T dx[NX];
     RMPC_UNROLL
     for (int i = 0; i < NX; ++i) dx[i] = T(0);  // x_1 is fixed
-    RMPC_UNROLL
-    for (int sl = 0; sl < SLOTS; ++sl) {
-      for (int kk = 0; kk < G; ++kk) {
-        const int k = kk + G * sl;
-        if (k >= N) break;
-        const StageShared<M, T>& st = S.st[k];
-        T dzk[NV];
-        RMPC_UNROLL
-        for (int i = 0; i < NX; ++i) dzk[i] = dx[i];
+    for (int k = 0; k < N; ++k) {
+      StageShared<M, T>& st = S.st[k];
+      T u[NU];
+      if (G == 1) {
         RMPC_UNROLL
         for (int j = 0; j < NU; ++j) {
-          T a = st.kff0[j] + mu * st.kff1[j];
+          T a = st.kff0(j) + mu * st.kff1(j);
           RMPC_UNROLL
-          for (int i = 0; i < NX; ++i) a += st.K[j * NX + i] * dx[i];
-          dzk[NX + j] = a;
+          for (int i = 0; i < NX; ++i) a += st.K(j, i) * dx[i];
+          u[j] = a;
         }
-        if (k < N - 1) {
+      } else {
+        const int j = g.lane < NU ? g.lane : 0;
+        T a = st.kff0(j) + mu * st.kff1(j), b = T(0);
+        RMPC_UNROLL
+        for (int i = 0; i + 1 < NX; i += 2) { a += st.K(j, i) * dx[i]; b += st.K(j, i + 1) * dx[i + 1]; }
+        if (NX % 2) a += st.K(j, NX - 1) * dx[NX - 1];
+        a += b;
+        RMPC_UNROLL
+        for (int l = 0; l < NU; ++l) u[l] = g.bcast(a, l);
+      }
+      RMPC_UNROLL
+      for (int i = 0; i < NX; ++i) st.dz[i] = dx[i];      // same value from every lane
+      RMPC_UNROLL
+      for (int j = 0; j < NU; ++j) st.dz[NX + j] = u[j];
+      if (k < N - 1) {
+        T dn[NX];
+        RMPC_UNROLL
+        for (int i = 0; i < NX; ++i) dn[i] = st.d[i];
+        RMPC_UNROLL
+        for (int j = 0; j < NV; ++j)
           RMPC_UNROLL
-          for (int i = 0; i < NX; ++i) dx[i] = st.d[i];
-          RMPC_UNROLL
-          for (int j = 0; j < NV; ++j)
-            RMPC_UNROLL
-            for (int e = 0; e < DS::n(j); ++e) dx[DS::row(j, e)] += DS::template val<T>(j, e, st.ABv) * dzk[j];
-        }
-        if (kk == g.lane) {
-          RMPC_UNROLL
-          for (int i = 0; i < NV; ++i) dz[sl][i] = dzk[i];
-          RMPC_UNROLL
-          for (int i = 0; i < NX; ++i) dxn[sl][i] = dx[i];
-        }
+          for (int e = 0; e < DS::n(j); ++e) dn[DS::row(j, e)] += DS::template val<T>(j, e, st.ABv) * (j < NX ? dx[j < NX ? j : 0] : u[j < NX ? 0 : j - NX]);
+        RMPC_UNROLL
+        for (int i = 0; i < NX; ++i) dx[i] = dn[i];
       }
     }
+    g.sync();
   }
 
-  RMPC_HD void row_dirs(int sl, T* gd) const {
+  RMPC_HD void row_dirs(int sl, int k, T* gd) const {
+    const T* sdz = S.st[k].dz;
     RMPC_UNROLL
     for (int r = 0; r < M::NGEO; ++r) {
       T a = T(0);
       RMPC_UNROLL
-      for (int i = 0; i < NQ; ++i) a += Gg[sl][r][i] * dz[sl][i];
+      for (int i = 0; i < NQ; ++i) a += Gg[sl][r][i] * sdz[i];
       gd[M::geo_row(r)] = a;
     }
     RMPC_UNROLL
-    for (int r = 0; r < M::NLIM; ++r) gd[M::lim_row(r)] = T(M::lim_sign(r)) * dz[sl][M::lim_var(r)];
+    for (int r = 0; r < M::NLIM; ++r) gd[M::lim_row(r)] = T(M::lim_sign(r)) * sdz[M::lim_var(r)];
   }
 
   // ---- the solve ----------------------------------------------------------------------------------
@@ -520,9 +546,9 @@ struct Ipm {
         const int k = g.lane + G * sl;
         if (k < N) {
           T gd[NH];
-          row_dirs(sl, gd);
+          row_dirs(sl, k, gd);
           RMPC_UNROLL
-          for (int i = 0; i < NV; ++i) dphi += S.st[k].qt0[i] * dz[sl][i];
+          for (int i = 0; i < NV; ++i) dphi += S.st[k].g0(i) * S.st[k].dz[i];
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];
@@ -559,7 +585,7 @@ struct Ipm {
             load_params<M, T>(pv, k, p);
             T zt[NV];
             RMPC_UNROLL
-            for (int i = 0; i < NV; ++i) zt[i] = S.st[k].z[i] + alpha * dz[sl][i];
+            for (int i = 0; i < NV; ++i) zt[i] = S.st[k].z[i] + alpha * S.st[k].dz[i];
             StageVal<M, T> sv;
             stage_values<M, T>(zt, p, sv);
             f += sv.f;
@@ -571,7 +597,7 @@ struct Ipm {
               if (!(stv >= (T(1) - tau) * s[sl][r])) {
                 bad = true;
 #if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
-                if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(s[sl][r]), double(lam[sl][r]), double(stv), double(s[sl][r] + alpha * gd[r]), double(alpha)); }
+                if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, k, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(s[sl][r]), double(lam[sl][r]), double(stv), double(s[sl][r] + alpha * gd[r]), double(alpha)); }
 #endif
               }
               la.mul(tmax(stv, T(1e-300)));
@@ -580,7 +606,7 @@ struct Ipm {
               T xn[NX];
               dyn_value<M, T>(zt, xn);
               RMPC_UNROLL
-              for (int i = 0; i < NX; ++i) theta += tabs(xn[i] - (S.st[k + 1].z[i] + alpha * dxn[sl][i]));
+              for (int i = 0; i < NX; ++i) theta += tabs(xn[i] - (S.st[k + 1].z[i] + alpha * S.st[k + 1].dz[i]));
             }
           }
         }
@@ -612,7 +638,7 @@ struct Ipm {
         const int k = g.lane + G * sl;
         if (k < N) {
           T gd[NH];
-          row_dirs(sl, gd);
+          row_dirs(sl, k, gd);
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];
@@ -631,7 +657,7 @@ struct Ipm {
             lam[sl][r] = ln;
           }
           RMPC_UNROLL
-          for (int i = 0; i < NV; ++i) S.st[k].z[i] += alpha * dz[sl][i];
+          for (int i = 0; i < NV; ++i) S.st[k].z[i] += alpha * S.st[k].dz[i];
         }
       }
       g.sync();

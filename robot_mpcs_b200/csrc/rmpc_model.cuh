@@ -54,9 +54,9 @@ __device__ __forceinline__ double trcp(double a) {
 }
 __device__ __forceinline__ double trsqrt(double a) {
   double r = double(rsqrtf(float(a)));
-  r = r * (1.5 - 0.5 * a * r * r);
-  r = r * (1.5 - 0.5 * a * r * r);
-  r = r * (1.5 - 0.5 * a * r * r);
+  const double ha = 0.5 * a;  // seed: 22 bits; two Newton steps: 43, then > 53 bits
+  r = r * (1.5 - ha * r * r);
+  r = r * (1.5 - ha * r * r);
   return r;
 }
 #else
