@@ -40,6 +40,10 @@ typedef struct {
   int control_mode; /* 0 "acc": action = u of stage 1; 1 "vel": action = z_2[nvar-2nu : nvar-nu] (mpcPlanner.py:275-278) */
   double tol_stat, tol_eq, tol_ineq, tol_comp;
   double mu0, mu_min, reg;
+  int creep_trigger; /* consecutive iterations whose first trial step left the interior of a nonlinear row before the
+                        barrier parameter is raised again (x10, at most mu0); 0 = monotone barrier only.  Default 3 */
+  int stall_window;  /* exit with -7 (no progress) when the optimality error has not dropped tenfold within this many
+                        iterations; 0 = never (default): only max_iter bounds the work of a problem */
 } rmpc_options;
 
 /* Per-problem diagnostics, structure of arrays of length B.  Device pointers for rmpc_solve_batch, host
@@ -74,6 +78,14 @@ int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x
 /* Same with HOST pointers: copies inputs to the device, solves, copies results back, synchronises. */
 int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
                           double* z_out, double* action_out, const rmpc_info* info);
+
+/* The same without the final synchronisation: enqueues H2D copies, the solve and the D2H copies on the handle's private
+ * stream and returns.  The host buffers must stay valid (and should be page-locked, otherwise the copies block) until
+ * rmpc_wait(s) returns.  One call in flight per handle; use two handles to overlap the copies of one batch with the
+ * solve of another (bench.py's end-to-end leg does). */
+int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                                double* z_out, double* action_out, const rmpc_info* info);
+int rmpc_wait(rmpc_solver* s);
 
 /* Warm start for `initialization: previous_plan` (mpcPlanner.py:215-226 shiftHorizon): x0[b][k] = z[b][k+1] for
  * k < N-1, x0[b][N-1] = z[b][N-1].  Device pointers, [B][N][nvar] each; in-place (x0 == z) is allowed. */

@@ -42,13 +42,15 @@ struct Options {
   double kappa;        // multipliers are kept above mu/(kappa s)
   double tau_min;      // fraction-to-boundary parameter tau = max(tau_min, 1 - mu)
   double lm0, lm_up, lm_down, lm_trigger;  // adaptive damping: start value, growth, decay, backtracks that trigger growth
+  double stall_window;                      // give up (-7) when the optimality error has not dropped 10x within this many iterations (0 = never)
+  double creep_trigger, creep_factor;      // consecutive boundary-cut full steps that trigger a barrier increase, and its factor
 };
 
 RMPC_HD Options default_options() {
   Options o;
   o.max_iter = 200; o.hessian = 1;
   o.tol_stat = 1e-6; o.tol_eq = 1e-8; o.tol_ineq = 1e-8; o.tol_comp = 1e-8;
-  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3;
+  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3; o.creep_trigger = 3; o.creep_factor = 10; o.stall_window = 0;
   return o;
 }
 
@@ -306,13 +308,16 @@ struct Ipm {
           else { const T h = st.Qs[NQD + (i < NDS ? 0 : i - NDS)]; a[i] = rhs ? q : (j == i ? h : T(0)); }
         }
         if (dyn) {
+          T abv[DS::NABV];
+          RMPC_UNROLL
+          for (int i = 0; i < DS::NVR * DS::NVC; ++i) abv[i] = st.ABv[i];
           T w[NX];
           RMPC_UNROLL
           for (int l = 0; l < NX; ++l) w[l] = S.PAB[l * LDF + j];
           RMPC_UNROLL
           for (int i = 0; i < NV; ++i)
             RMPC_UNROLL
-            for (int e = 0; e < DS::n(i); ++e) a[i] += DS::template val<T>(i, e, st.ABv) * w[DS::row(i, e)];
+            for (int e = 0; e < DS::n(i); ++e) a[i] += DS::template val<T>(i, e, abv) * w[DS::row(i, e)];
         }
         RMPC_UNROLL
         for (int i = 0; i < NV; ++i) S.F[i * LDF + j] = a[i];  // above the diagonal: junk that nobody reads
@@ -389,11 +394,14 @@ struct Ipm {
         if (k > 0) {
           StageShared<M, T>& sp = S.st[k - 1];
           if (i < 2) sp.nu01[i] = nui;
+          T abv[DS::NABV];
+          RMPC_UNROLL
+          for (int j = 0; j < DS::NVR * DS::NVC; ++j) abv[j] = sp.ABv[j];
           RMPC_UNROLL
           for (int j = 0; j < NV; ++j) {
             T a = T(0);
             RMPC_UNROLL
-            for (int e = 0; e < DS::n(j); ++e) a += DS::template val<T>(j, e, sp.ABv) * Pi[DS::row(j, e)];
+            for (int e = 0; e < DS::n(j); ++e) a += DS::template val<T>(j, e, abv) * Pi[DS::row(j, e)];
             S.PAB[i * LDF + j] = a;
           }
           T a = p0;
@@ -496,7 +504,7 @@ struct Ipm {
           const T shift = hv >= T(opt.delta) ? T(0) : T(opt.delta) - hv;
           sh[sl][r] = shift;
           s[sl][r] = hv + shift;
-          lam[sl][r] = mu / (hv + shift);
+          lam[sl][r] = mu * trcp(hv + shift);
         }
       }
     }
@@ -505,6 +513,8 @@ struct Ipm {
     Red<T> so;
     so.f = so.res_stat = so.res_eq = so.comp_max = so.shift_max = T(0);
     T rho_pen = T(1);
+    int ncreep = 0, it_ref = 0;
+    T err_ref = T(1e300);
     T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
     if (g.any(pole0)) { info.exitflag = -8; it = opt.max_iter + 1; }
     for (; it <= opt.max_iter; ++it) {
@@ -520,18 +530,24 @@ struct Ipm {
       if (!so.finite || !so.ok) { info.exitflag = so.ok ? -6 : -5; break; }
       if (so.comp_max > T(1e15) || so.s_min < T(1e-13)) { info.exitflag = -7; break; }  // multipliers diverge: locally infeasible
       // ---- convergence test (IPOPT scaling of the dual residual)
-      const T sd = tmax(T(100), so.mult_sum / T(N * (NH + NX))) / T(100);
-      if (so.res_stat / sd <= T(opt.tol_stat) && so.res_eq <= T(opt.tol_eq) && so.shift_max <= T(opt.tol_ineq) &&
-          so.comp_max / sd <= T(opt.tol_comp)) {
+      const T sd = tmax(T(100), so.mult_sum * T(1.0 / (N * (NH + NX)))) * T(0.01);
+      const T isd = trcp(sd);
+      if (so.res_stat * isd <= T(opt.tol_stat) && so.res_eq <= T(opt.tol_eq) && so.shift_max <= T(opt.tol_ineq) &&
+          so.comp_max * isd <= T(opt.tol_comp)) {
         info.exitflag = 1;
         break;
       }
       if (it == opt.max_iter) break;
+      {  // stall detection on the optimality error of the original problem
+        const T err = tmax(tmax(so.res_stat, so.comp_max) * isd, tmax(so.res_eq, so.shift_max));
+        if (err < T(0.1) * err_ref) { err_ref = err; it_ref = it; }
+        if (opt.stall_window > 0 && it - it_ref >= int(opt.stall_window)) { info.exitflag = -7; break; }
+      }
       // ---- monotone barrier update (Fiacco-McCormick as in IPOPT): shrink mu while the current barrier
       //      problem is solved to within kappa_eps * mu
       for (int rep = 0; rep < 8; ++rep) {
         const T cmu = tmax(so.comp_max - mu, mu - so.comp_min);
-        const T emu = tmax(tmax(so.res_stat / sd, cmu / sd), tmax(so.res_eq, so.shift_max));
+        const T emu = tmax(tmax(so.res_stat, cmu) * isd, tmax(so.res_eq, so.shift_max));
         if (emu <= T(10) * mu && mu > T(opt.mu_min)) {
           const T m15 = mu * tsqrt(mu);
           mu = tmax(T(opt.mu_min), tmin(T(0.2) * mu, m15));
@@ -562,9 +578,9 @@ struct Ipm {
         }
       }
       rp = g.max(rp); rd = g.max(rd); dphi = g.sum(dphi);
-      const T ap = rp > tau ? tau / rp : T(1), ad = rd > tau ? tau / rd : T(1);
+      const T ap = rp > tau ? tau * trcp(rp) : T(1), ad = rd > tau ? tau * trcp(rd) : T(1);
       if (so.theta > T(1e-14)) {
-        const T need = dphi / (T(0.9) * so.theta);
+        const T need = dphi * trcp(T(0.9) * so.theta);
         if (need > rho_pen) rho_pen = need * T(1.1) + T(1e-3);
       }
       const T phi0 = so.f - mu * so.logs + rho_pen * so.theta;
@@ -573,6 +589,7 @@ struct Ipm {
       T alpha = ap;
       bool accepted = false;
       int nls = 0;
+      bool cut = false;  // the first trial left the interior of a nonlinear row
       for (int ls = 0; ls < 30; ++ls) {
         T f = T(0), theta = T(0);
         LogAcc<T> la;
@@ -620,6 +637,7 @@ struct Ipm {
 #endif
         if (!bad && (phi == phi) && phi <= phi0 + T(1e-4) * alpha * slope + tol_phi) { accepted = true; break; }
         alpha *= T(0.5);
+        if (ls == 0 && bad) cut = true;
         ++nls;
       }
 #if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
@@ -628,11 +646,14 @@ struct Ipm {
              double(so.shift_max), double(ap), double(ad), double(alpha), double(dphi), double(rho_pen), double(slope), int(accepted), int(exact));
 #endif
       if (!accepted) { info.exitflag = -7; break; }
+      ncreep = cut ? ncreep + 1 : 0;
+      if (opt.creep_trigger > 0 && ncreep >= int(opt.creep_trigger)) { mu = tmin(mu * T(opt.creep_factor), T(opt.mu0)); ncreep = 0; }
       if (nls >= int(opt.lm_trigger)) lm = tmax(lm * T(opt.lm_up), T(opt.lm0));
       else if (nls == 0) lm = lm * T(opt.lm_down) < T(0.1) * T(opt.lm0) ? T(0) : lm * T(opt.lm_down);
       // ---- take the step
       g.sync();  // every lane has read its neighbour's z for this line search
       const T adu = tmin(ad, T(1));
+      const T ikappa = T(1.0 / opt.kappa);
       RMPC_UNROLL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
@@ -652,7 +673,7 @@ struct Ipm {
             }
             T ln = lr + adu * dlr;
             const T mus = mu * trcp(sn);
-            ln = tmin(tmax(ln, mus / T(opt.kappa)), T(1e10) * mus);
+            ln = tmin(tmax(ln, mus * ikappa), T(1e10) * mus);
             s[sl][r] = sn;
             lam[sl][r] = ln;
           }

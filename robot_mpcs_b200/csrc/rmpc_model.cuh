@@ -32,7 +32,8 @@ namespace rmpc {
 
 template <class T> RMPC_HD T tmax(T a, T b) { return a > b ? a : b; }
 template <class T> RMPC_HD T tmin(T a, T b) { return a < b ? a : b; }
-template <class T> RMPC_HD T tabs(T a) { return a < T(0) ? -a : a; }
+RMPC_HD float tabs(float a) { return fabsf(a); }
+RMPC_HD double tabs(double a) { return fabs(a); }
 RMPC_HD float tsqrt(float a) { return sqrtf(a); }
 RMPC_HD double tsqrt(double a) { return sqrt(a); }
 RMPC_HD float tlog(float a) { return logf(a); }

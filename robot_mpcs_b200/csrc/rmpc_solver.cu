@@ -47,6 +47,7 @@ struct rmpc_solver {
   // device staging for the host entry point
   double *h_xinit, *h_x0, *h_params, *h_z, *h_action, *h_res;
   int* h_flag;
+  cudaStream_t hstream;  // private stream of the host entry points
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -129,6 +130,7 @@ static Options to_core(const rmpc_options& o) {
   c.max_iter = o.max_iter; c.hessian = o.hessian;
   c.tol_stat = o.tol_stat; c.tol_eq = o.tol_eq; c.tol_ineq = o.tol_ineq; c.tol_comp = o.tol_comp;
   c.mu0 = o.mu0; c.mu_min = o.mu_min; c.reg = o.reg;
+  c.creep_trigger = o.creep_trigger; c.stall_window = o.stall_window;
   return c;
 }
 
@@ -149,6 +151,7 @@ void rmpc_default_options(rmpc_options* o) {
   o->max_iter = c.max_iter; o->hessian = c.hessian; o->precision = 0; o->control_mode = 0;
   o->tol_stat = c.tol_stat; o->tol_eq = c.tol_eq; o->tol_ineq = c.tol_ineq; o->tol_comp = c.tol_comp;
   o->mu0 = c.mu0; o->mu_min = c.mu_min; o->reg = c.reg;
+  o->creep_trigger = int(c.creep_trigger); o->stall_window = int(c.stall_window);
 }
 
 constexpr int kCounterSlots = 64;
@@ -157,6 +160,7 @@ static int free_all(rmpc_solver* s) {
   cudaFree(s->counter); cudaFree(s->z_tmp);
   cudaFree(s->d_idx); cudaFree(s->h_xinit); cudaFree(s->h_x0); cudaFree(s->h_params); cudaFree(s->h_z);
   cudaFree(s->h_action); cudaFree(s->h_res); cudaFree(s->h_flag);
+  if (s->hstream) cudaStreamDestroy(s->hstream);
   return 0;
 }
 
@@ -191,6 +195,7 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
   s->sm_count = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&s->hstream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
   return s;
 }
 
@@ -203,7 +208,8 @@ void rmpc_destroy(rmpc_solver* s) {
 
 int rmpc_set_options(rmpc_solver* s, const rmpc_options* o) {
   if (!s || !o) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
-  if (o->precision < 0 || o->precision > 1 || o->hessian < 0 || o->hessian > 1 || o->control_mode < 0 || o->control_mode > 1) {
+  if (o->precision < 0 || o->precision > 1 || o->hessian < 0 || o->hessian > 1 || o->control_mode < 0 || o->control_mode > 1 ||
+      o->creep_trigger < 0 || o->stall_window < 0) {
     snprintf(g_err, sizeof g_err, "option out of range");
     return -1;
   }
@@ -255,14 +261,14 @@ static int ensure_host_staging(rmpc_solver* s) {
   return 0;
 }
 
-int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
-                          double* z_out, double* action_out, const rmpc_info* info) {
+int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                                double* z_out, double* action_out, const rmpc_info* info) {
   if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
   CK(cudaSetDevice(s->device));
   if (ensure_host_staging(s)) return -1;
   const size_t b = (size_t)B, mb = (size_t)s->max_batch;
-  cudaStream_t st = 0;
+  cudaStream_t st = s->hstream;
   CK(cudaMemcpyAsync(s->h_xinit, xinit, sizeof(double) * b * M::NX, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(s->h_x0, x0, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(s->h_params, params, sizeof(double) * b * M::N * M::NPAR, cudaMemcpyHostToDevice, st));
@@ -287,8 +293,20 @@ int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const doub
     if (info->res_ineq) CK(cudaMemcpyAsync(info->res_ineq, dinf.res_ineq, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
     if (info->res_comp) CK(cudaMemcpyAsync(info->res_comp, dinf.res_comp, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
   }
-  CK(cudaStreamSynchronize(st));
   return 0;
+}
+
+int rmpc_wait(rmpc_solver* s) {
+  if (!s) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
+  CK(cudaSetDevice(s->device));
+  CK(cudaStreamSynchronize(s->hstream));
+  return 0;
+}
+
+int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                          double* z_out, double* action_out, const rmpc_info* info) {
+  if (rmpc_solve_batch_host_async(s, B, xinit, x0, params, z_out, action_out, info)) return -1;
+  return rmpc_wait(s);
 }
 
 int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void* stream) {

@@ -29,7 +29,8 @@ class RmpcOptions(ctypes.Structure):
     _fields_ = [("max_iter", ctypes.c_int), ("hessian", ctypes.c_int), ("precision", ctypes.c_int),
                 ("control_mode", ctypes.c_int), ("tol_stat", ctypes.c_double), ("tol_eq", ctypes.c_double),
                 ("tol_ineq", ctypes.c_double), ("tol_comp", ctypes.c_double), ("mu0", ctypes.c_double),
-                ("mu_min", ctypes.c_double), ("reg", ctypes.c_double)]
+                ("mu_min", ctypes.c_double), ("reg", ctypes.c_double), ("creep_trigger", ctypes.c_int),
+                ("stall_window", ctypes.c_int)]
 
 
 class RmpcInfo(ctypes.Structure):
@@ -39,7 +40,7 @@ class RmpcInfo(ctypes.Structure):
 
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
-           "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_host", "rmpc_shift_horizon",
+           "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_shift_horizon",
            "rmpc_set_params", "rmpc_launch_count"]
 
 
@@ -64,6 +65,8 @@ def load_library(solver_dir: str) -> ctypes.CDLL:
     lib.rmpc_get_options.argtypes = [ctypes.c_void_p, ctypes.POINTER(RmpcOptions)]
     lib.rmpc_solve_batch.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo), ctypes.c_void_p]
     lib.rmpc_solve_batch_host.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo)]
+    lib.rmpc_solve_batch_host_async.argtypes = lib.rmpc_solve_batch_host.argtypes
+    lib.rmpc_wait.argtypes = [ctypes.c_void_p]
     lib.rmpc_shift_horizon.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.rmpc_set_params.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_int,
                                     ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
@@ -128,12 +131,12 @@ class Solver:
             pass
 
     # -- batched solve -----------------------------------------------------------------------
-    def solve_batch(self, xinit, x0, params, want_z=True, want_info=True):
+    def solve_batch(self, xinit, x0, params, want_z=True, want_info=True, block=True):
         """xinit[B,nx], x0[B,N,nvar], params[B,N,npar] float64.  CUDA torch tensors -> device path (asynchronous on
         the current stream, returns CUDA tensors); numpy arrays / CPU tensors -> host path (returns numpy)."""
         if torch is not None and isinstance(xinit, torch.Tensor) and xinit.is_cuda:
             return self._solve_device(xinit, x0, params, want_z, want_info)
-        return self._solve_host(np.asarray(xinit), np.asarray(x0), np.asarray(params), want_z, want_info)
+        return self._solve_host(np.asarray(xinit), np.asarray(x0), np.asarray(params), want_z, want_info, block)
 
     def _solve_device(self, xinit, x0, params, want_z, want_info):
         B = xinit.shape[0]
@@ -162,7 +165,12 @@ class Solver:
             raise SolverError("rmpc_solve_batch failed: " + self._err())
         return out
 
-    def _solve_host(self, xinit, x0, params, want_z, want_info):
+    def wait(self):
+        """Block until the last `solve_batch(..., block=False)` on host buffers has delivered its results."""
+        if self.lib.rmpc_wait(self._h) != 0:
+            raise SolverError("rmpc_wait failed: " + self._err())
+
+    def _solve_host(self, xinit, x0, params, want_z, want_info, block=True):
         xinit = np.ascontiguousarray(xinit, dtype=np.float64).reshape(-1, self.nx)
         B = xinit.shape[0]
         self._ensure(B)
@@ -179,7 +187,9 @@ class Solver:
                 out[k] = np.empty(B)
             for k, _ in RmpcInfo._fields_:
                 setattr(info, k, out[k].ctypes.data)
-        rc = self.lib.rmpc_solve_batch_host(self._h, B, xinit.ctypes.data, x0.ctypes.data, params.ctypes.data,
+        self._keep = (xinit, x0, params)  # the copies are asynchronous: keep the (possibly converted) inputs alive
+        fn = self.lib.rmpc_solve_batch_host if block else self.lib.rmpc_solve_batch_host_async
+        rc = fn(self._h, B, xinit.ctypes.data, x0.ctypes.data, params.ctypes.data,
                                             z.ctypes.data if want_z else None, act.ctypes.data,
                                             ctypes.byref(info) if want_info else None)
         if rc != 0:

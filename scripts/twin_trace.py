@@ -5,7 +5,7 @@ sys.path.insert(0, ROOT)
 from robot_mpcs_b200 import scenarios as sc
 from oracle.build_twin import Twin
 S = os.path.join(ROOT, 'robot_mpcs_b200', 'solvers')
-W = {"pr": ("pointRobot_n3_005_H20_noSlack", sc.point_robot_sweep, 2048), "boxer": ("boxer_n3_01_H30_noSlack", sc.boxer_radial, 1024),
+W = {"pr": ("pointRobot_n3_005_H20_noSlack", sc.point_robot_sweep, 2048), "boxer": ("boxer_n3_01_H30_noSlack", sc.boxer_radial, int(os.environ.get("NB", 1024))),
      "panda": ("panda_n7_005_H20_noSlack", sc.panda, 256), "sm": ("boxer_n3_01_H40_noSlack", sc.boxer_supermarket, 512)}
 sdir, gen, B = W[sys.argv[1]]
 b = int(sys.argv[2])
