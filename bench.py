@@ -207,8 +207,10 @@ def run_ours(args):
     sdir, _, defB, f_iter, desc = WORKLOADS[args.workload]
     B = args.batch or defB
     solver = Solver.from_directory(os.path.join(SOLVERS, sdir), device=local_rank, max_batch=B)
-    solver.set_options(precision=args.precision, hessian=args.hessian)
-    nsets = 2  # alternate input sets; L2 is flushed between steps anyway
+    solver.set_options(precision=args.precision, hessian=args.hessian, stall_window=args.stall_window)
+    set_bytes = 8 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar)
+    # rotating input sets whose total exceeds the 126 MB L2, so that no step finds its inputs cached
+    nsets = int(min(16, max(2, -(-160e6 // set_bytes))))
     sets = []
     for i in range(nsets):
         s = make_inputs(args.workload, B, seed=1000 * rank + i)
@@ -216,7 +218,8 @@ def run_ours(args):
         devt = {k: v.to(dev) for k, v in host.items()}
         sets.append((host, devt))
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # 256 MB > 126 MB L2
-    nu = solver.nu
+    nstreams = max(1, args.streams)
+    streams = [torch.cuda.Stream(dev) for _ in range(nstreams)]
 
     def step_device(i):
         _, d = sets[i % nsets]
@@ -229,33 +232,41 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def run_steps(n):
+        """n batched solves, step i on stream i % nstreams (consecutive batches overlap: the stragglers of one batch no
+        longer idle the GPU); returns device time from the first launch to the last completion, and the per-step results."""
+        main = torch.cuda.current_stream(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(main)
+        for st in streams:
+            st.wait_event(e0)
+        res = []
+        for i in range(n):
+            with torch.cuda.stream(streams[i % nstreams]):
+                res.append(step_device(i)[0])
+        for st in streams:
+            ev = torch.cuda.Event()
+            ev.record(st)
+            main.wait_event(ev)
+        e1.record(main)
+        return e0, e1, res
+
     # ---- device-resident throughput ("value")
-    for i in range(args.warmup):
-        step_device(i)
+    run_steps(args.warmup)
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     launches0 = solver.launch_count()
-    ev = []
-    conv_total, iters_total, nsolved = 0, 0, 0
     t_wall = time.perf_counter()
-    for i in range(args.steps):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        r, f, it = step_device(i)
-        e1.record()
-        ev.append((e0, e1, r))
+    e0, e1, results = run_steps(args.steps)
     barrier()
     t_wall = time.perf_counter() - t_wall
     launches = solver.launch_count() - launches0
-    dev_ms = [a.elapsed_time(b) for a, b, _ in ev]
-    for _, _, r in ev:
-        conv_total += int((r["exitflag"] == 1).sum())
-        iters_total += int(r["iters"].sum())
-        nsolved += B
-    total_ms = torch.tensor([sum(dev_ms)], dtype=torch.float64, device=dev)
+    conv_total = sum(int((r["exitflag"] == 1).sum()) for r in results)
+    iters_total = sum(int(r["iters"].sum()) for r in results)
+    nsolved = B * len(results)
+    total_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     conv_t = torch.tensor([conv_total, iters_total, nsolved], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
@@ -264,12 +275,11 @@ def run_ours(args):
     total_s = float(total_ms) * 1e-3
     value = float(conv_t[0]) / total_s
 
-    # ---- solve kernel alone (roofline): events around the kernel launch only, own inputs > no reuse (L2 flushed)
+    # ---- one batch alone (roofline of the solve kernel, and the latency of a whole batch): L2 flushed, events around the launch
     kern_ms = []
     _, d = sets[0]
     for i in range(max(3, min(args.steps, 10))):
         flush.zero_()
-        # pack happens inside solve_batch; time the whole call minus nothing: the solve kernel is >95% of it (ncu launch list)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         rr = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
@@ -280,19 +290,31 @@ def run_ours(args):
     flops = float(rr["iters"].sum()) * f_iter
     bytes_alg = 8.0 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar) + 8.0 * B * (solver.nu + 1) + 4.0 * B * 2
 
-    # ---- end to end through the host entry point (pinned host buffers -> H2D -> solve -> D2H)
-    e2e_times, e2e_conv = [], 0
-    h, _ = sets[0]
-    hx, h0, hp = (h[k].numpy() for k in ("xinit", "x0", "params"))
-    for i in range(2):
-        solver.solve_batch(hx, h0, hp, want_z=False, want_info=True)
+    # ---- end to end through the host entry points (pinned host buffers -> H2D -> solve -> D2H), two handles in flight
+    nh = min(nstreams, 3)
+    hsolvers = [solver] + [Solver.from_directory(os.path.join(SOLVERS, sdir), device=local_rank, max_batch=B) for _ in range(nh - 1)]
+    for hs in hsolvers[1:]:
+        hs.set_options(precision=args.precision, hessian=args.hessian, stall_window=args.stall_window)
+    hnp = [{k: v.numpy() for k, v in h.items()} for h, _ in sets]
+
+    def e2e_run(n):
+        pend, conv = [None] * nh, 0
+        for i in range(n + nh):
+            j = i % nh
+            if pend[j] is not None:
+                hsolvers[j].wait()
+                conv += int((pend[j]["exitflag"] == 1).sum())
+                pend[j] = None
+            if i < n:
+                hh = hnp[i % nsets]
+                pend[j] = hsolvers[j].solve_batch(hh["xinit"], hh["x0"], hh["params"], want_z=False, want_info=True, block=False)
+        return conv
+
+    e2e_run(2)
     barrier()
-    e2e_steps = max(3, min(args.steps, 10))
+    e2e_steps = max(4, min(args.steps, 10))
     t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        hh, _ = sets[i % nsets]
-        r = solver.solve_batch(hh["xinit"].numpy(), hh["x0"].numpy(), hh["params"].numpy(), want_z=False, want_info=True)
-        e2e_conv += int((r["exitflag"] == 1).sum())
+    e2e_conv = e2e_run(e2e_steps)
     barrier()
     e2e_s = time.perf_counter() - t0
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -300,7 +322,7 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
         dist.all_reduce(e2e_c, op=dist.ReduceOp.SUM)
-    h2d = 8 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar)
+    h2d = set_bytes
     d2h = 8 * B * (solver.nu + 5) + 4 * B * 2
 
     lat = None
@@ -328,7 +350,8 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64" if args.precision == 0 else "f64+f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "batch_per_gpu": B, "global_batch": B * world,
-                       "l2": "flushed between steps (256 MB write)", "hessian": "exact+GN fallback" if args.hessian else "gauss-newton",
+                       "l2": f"{nsets} rotating input sets of {set_bytes / 1e6:.0f} MB (> 126 MB L2 in total); single-batch timing with L2 flushed (256 MB write)",
+                       "streams": nstreams, "stall_window": args.stall_window, "hessian": "exact+GN fallback" if args.hessian else "gauss-newton",
                        "tolerances": {k: v for k, v in solver.options().items() if k.startswith("tol")},
                        "parallelism": f"scenario-sharded x{world}, all_gather of action/exitflag/iters per step"},
             "converged_fraction": float(conv_t[0] / conv_t[2]), "mean_iters": float(conv_t[1] / conv_t[2]),
@@ -336,11 +359,11 @@ def run_ours(args):
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": (achieved_tf / fp64_peak) if fp64_peak else None, "traffic": None,
                          "peak_source": "measured in this run (csrc/peak_fma.cu DFMA chains); MEASURED_PEAKS.json has no FP64 figure",
-                         "fp32_peak_measured": fp32_peak, "kernel_ms": k_ms,
+                         "fp32_peak_measured": fp32_peak, "kernel_ms": k_ms, "single_batch_solves_per_s": float((rr["exitflag"] == 1).sum()) / (k_ms * 1e-3),
                          "flops_per_launch": flops, "hbm": {"achieved": bytes_alg / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                                                             "frac": bytes_alg / (k_ms * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes": bytes_alg}},
             "e2e": {"value": float(e2e_c) / float(e2e_t), "unit": "converged solves/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "api": "rmpc_solve_batch_host (pinned host buffers)"},
+                    "steps": e2e_steps, "api": f"rmpc_solve_batch_host_async + rmpc_wait on {nh} handle(s), pinned host buffers"},
             "clocks": clocks,
         }
         if base is not None:
@@ -366,6 +389,8 @@ def main():
     ap.add_argument("--hessian", type=int, default=1)
     ap.add_argument("--ref-sample", type=int, default=4096, help="scenarios per CPU-baseline pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--streams", type=int, default=4, help="CUDA streams the consecutive batches are spread over (1 = strictly one batch at a time)")
+    ap.add_argument("--stall-window", type=int, default=0, help="rmpc_options.stall_window (0 = off, the default)")
     ap.add_argument("--latency-samples", type=int, default=300, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

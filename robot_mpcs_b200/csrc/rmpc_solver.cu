@@ -48,6 +48,12 @@ struct rmpc_solver {
   double *h_xinit, *h_x0, *h_params, *h_z, *h_action, *h_res;
   int* h_flag;
   cudaStream_t hstream;  // private stream of the host entry points
+  // page-locked landing zone of the asynchronous D2H copies, and the caller's buffers they are handed to in rmpc_wait
+  double *p_z, *p_action, *p_res;
+  int* p_flag;
+  int pend_B;
+  double *u_z, *u_action;
+  rmpc_info u_info;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -161,6 +167,7 @@ static int free_all(rmpc_solver* s) {
   cudaFree(s->d_idx); cudaFree(s->h_xinit); cudaFree(s->h_x0); cudaFree(s->h_params); cudaFree(s->h_z);
   cudaFree(s->h_action); cudaFree(s->h_res); cudaFree(s->h_flag);
   if (s->hstream) cudaStreamDestroy(s->hstream);
+  cudaFreeHost(s->p_z); cudaFreeHost(s->p_action); cudaFreeHost(s->p_res); cudaFreeHost(s->p_flag);
   return 0;
 }
 
@@ -258,6 +265,9 @@ static int ensure_host_staging(rmpc_solver* s) {
   CK(cudaMalloc(&s->h_action, sizeof(double) * mb * M::NU));
   CK(cudaMalloc(&s->h_res, sizeof(double) * mb * 5));
   CK(cudaMalloc(&s->h_flag, sizeof(int) * mb * 2));
+  CK(cudaMallocHost(&s->p_action, sizeof(double) * mb * M::NU));
+  CK(cudaMallocHost(&s->p_res, sizeof(double) * mb * 5));
+  CK(cudaMallocHost(&s->p_flag, sizeof(int) * mb * 2));
   return 0;
 }
 
@@ -265,6 +275,7 @@ int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, cons
                                 double* z_out, double* action_out, const rmpc_info* info) {
   if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
+  if (s->pend_B) { snprintf(g_err, sizeof g_err, "a host solve is already in flight on this handle: call rmpc_wait first"); return -1; }
   CK(cudaSetDevice(s->device));
   if (ensure_host_staging(s)) return -1;
   const size_t b = (size_t)B, mb = (size_t)s->max_batch;
@@ -282,17 +293,18 @@ int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, cons
   if (rmpc_solve_batch(s, B, s->h_xinit, s->h_x0, s->h_params, z_out ? s->h_z : nullptr,
                        action_out ? s->h_action : nullptr, info ? &dinf : nullptr, st))
     return -1;
-  if (z_out) CK(cudaMemcpyAsync(z_out, s->h_z, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyDeviceToHost, st));
-  if (action_out) CK(cudaMemcpyAsync(action_out, s->h_action, sizeof(double) * b * M::NU, cudaMemcpyDeviceToHost, st));
-  if (info) {
-    if (info->exitflag) CK(cudaMemcpyAsync(info->exitflag, dinf.exitflag, sizeof(int) * b, cudaMemcpyDeviceToHost, st));
-    if (info->iters) CK(cudaMemcpyAsync(info->iters, dinf.iters, sizeof(int) * b, cudaMemcpyDeviceToHost, st));
-    if (info->obj) CK(cudaMemcpyAsync(info->obj, dinf.obj, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
-    if (info->res_stat) CK(cudaMemcpyAsync(info->res_stat, dinf.res_stat, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
-    if (info->res_eq) CK(cudaMemcpyAsync(info->res_eq, dinf.res_eq, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
-    if (info->res_ineq) CK(cudaMemcpyAsync(info->res_ineq, dinf.res_ineq, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
-    if (info->res_comp) CK(cudaMemcpyAsync(info->res_comp, dinf.res_comp, sizeof(double) * b, cudaMemcpyDeviceToHost, st));
+  if (z_out) {
+    if (!s->p_z) CK(cudaMallocHost(&s->p_z, sizeof(double) * mb * M::N * M::NVAR));
+    CK(cudaMemcpyAsync(s->p_z, s->h_z, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyDeviceToHost, st));
   }
+  if (action_out) CK(cudaMemcpyAsync(s->p_action, s->h_action, sizeof(double) * b * M::NU, cudaMemcpyDeviceToHost, st));
+  if (info) {
+    CK(cudaMemcpyAsync(s->p_flag, s->h_flag, sizeof(int) * (mb + b), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(s->p_res, s->h_res, sizeof(double) * (4 * mb + b), cudaMemcpyDeviceToHost, st));
+  }
+  s->pend_B = B; s->u_z = z_out; s->u_action = action_out;
+  memset(&s->u_info, 0, sizeof s->u_info);
+  if (info) s->u_info = *info;
   return 0;
 }
 
@@ -300,6 +312,17 @@ int rmpc_wait(rmpc_solver* s) {
   if (!s) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   CK(cudaSetDevice(s->device));
   CK(cudaStreamSynchronize(s->hstream));
+  if (!s->pend_B) return 0;
+  const size_t b = (size_t)s->pend_B, mb = (size_t)s->max_batch;
+  s->pend_B = 0;
+  if (s->u_z) memcpy(s->u_z, s->p_z, sizeof(double) * b * M::N * M::NVAR);
+  if (s->u_action) memcpy(s->u_action, s->p_action, sizeof(double) * b * M::NU);
+  const rmpc_info& u = s->u_info;
+  if (u.exitflag) memcpy(u.exitflag, s->p_flag, sizeof(int) * b);
+  if (u.iters) memcpy(u.iters, s->p_flag + mb, sizeof(int) * b);
+  double* dst[5] = {u.obj, u.res_stat, u.res_eq, u.res_ineq, u.res_comp};
+  for (int i = 0; i < 5; ++i)
+    if (dst[i]) memcpy(dst[i], s->p_res + i * mb, sizeof(double) * b);
   return 0;
 }
 
