@@ -176,7 +176,8 @@ struct Ipm {
   const Options& opt;
 
   // per-lane state of the stages this lane owns
-  T lam[SLOTS][NH], s[SLOTS][NH], sh[SLOTS][NH], htr[SLOTS][NH];
+  T lam[SLOTS][NH], s[SLOTS][NH];
+  float sh[SLOTS][NH];  // shifts of the rows that started infeasible (any positive number works: single precision is enough)
   T Gg[SLOTS][NGEO1][NQ];
 
   RMPC_HD Ipm(const Group<G>& g_, ProblemShared<M, T>& S_, const ParamView<T>& pv_, const Options& o_) : g(g_), S(S_), pv(pv_), opt(o_) {}
@@ -208,8 +209,8 @@ struct Ipm {
           cmax = tmax(cmax, sr * lr);
           cmin = tmin(cmin, sr * lr);
           msum += lr;
-          shmax = tmax(shmax, sh[sl][r]);
-          if (sh[sl][r] > T(0)) smin = tmin(smin, sr);  // slack of a row that is still shifted
+          shmax = tmax(shmax, T(sh[sl][r]));
+          if (sh[sl][r] > 0.0f) smin = tmin(smin, sr - T(1e-6f * sh[sl][r]));  // a slack this small next to its shift cannot recover  // slack of a row that is still shifted
         }
         RMPC_UNROLL
         for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lam[sl][M::geo_row(r)]; }
@@ -501,10 +502,10 @@ struct Ipm {
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
           const T hv = sv.h[r];
-          const T shift = hv >= T(opt.delta) ? T(0) : T(opt.delta) - hv;
+          const float shift = hv >= T(opt.delta) ? 0.0f : float(T(opt.delta) - hv);
           sh[sl][r] = shift;
-          s[sl][r] = hv + shift;
-          lam[sl][r] = mu * trcp(hv + shift);
+          s[sl][r] = hv + T(shift);
+          lam[sl][r] = mu * trcp(hv + T(shift));
         }
       }
     }
@@ -609,8 +610,8 @@ struct Ipm {
             bad = bad || sv.pole;
             RMPC_UNROLL
             for (int r = 0; r < NH; ++r) {
-              const T stv = sv.h[r] + sh[sl][r];
-              htr[sl][r] = sv.h[r];
+              const T stv = sv.h[r] + T(sh[sl][r]);
+              S.st[k].Qs[r] = sv.h[r];  // kept for the update of s once the trial is accepted (K and kff are dead by now)
               if (!(stv >= (T(1) - tau) * s[sl][r])) {
                 bad = true;
 #if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
@@ -665,10 +666,11 @@ struct Ipm {
             const T sr = s[sl][r], lr = lam[sl][r];
             const T rs = trcp(sr);
             const T dlr = mu * rs - lr - (lr * rs) * gd[r];
-            T sn = htr[sl][r] + sh[sl][r];
-            if (sh[sl][r] > T(0)) {  // shrink the shift of a row that started infeasible, keeping s >= s/2
-              const T shn = tmax(T(0), sh[sl][r] - T(0.5) * sn);
-              sn -= sh[sl][r] - shn;
+            const T sho = T(sh[sl][r]);
+            T sn = S.st[k].Qs[r] + sho;
+            if (sho > T(0)) {  // shrink the shift of a row that started infeasible, keeping s >= s/2
+              const float shn = float(tmax(T(0), sho - T(0.5) * sn));
+              sn -= sho - T(shn);
               sh[sl][r] = shn;
             }
             T ln = lr + adu * dlr;
