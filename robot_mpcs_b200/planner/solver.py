@@ -115,7 +115,9 @@ class Solver:
                 raise KeyError(k)
             setattr(self._opts, k, v)
         if self.lib.rmpc_set_options(self._h, ctypes.byref(self._opts)) != 0:
-            raise SolverError(self._err())
+            msg = self._err()
+            self.lib.rmpc_get_options(self._h, ctypes.byref(self._opts))  # keep the mirror equal to what the handle holds
+            raise SolverError(msg)
 
     def options(self) -> dict:
         return {n: getattr(self._opts, n) for n, _ in RmpcOptions._fields_}

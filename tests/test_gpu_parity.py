@@ -182,3 +182,55 @@ def test_full_size_properties(built):
     assert float(defect) < 1e-7
     assert float(m.ineq(Z, Pm).min()) > -1e-7
     assert float(Z.abs().max()) <= 100.0          # the +-100 box of the NLP is inactive, hence satisfied
+
+
+def test_async_host_entry_point_two_handles(built):
+    """rmpc_solve_batch_host_async / rmpc_wait: two handles in flight give the same bits as the blocking call, and a
+    second enqueue on a busy handle is refused."""
+    from robot_mpcs_b200.planner.solver import SolverError
+    sdir = "pointRobot_n3_005_H20_noSlack"
+    B = 257
+    sa, sb = (sc.point_robot_sweep(_pm(sdir), B, seed=s) for s in (11, 12))
+    h1, h2 = _solver(sdir, B), _solver(sdir, B)
+    ra = h1.solve_batch(sa["xinit"], sa["x0"], sa["params"])
+    rb = h1.solve_batch(sb["xinit"], sb["x0"], sb["params"])
+    pa = h1.solve_batch(sa["xinit"], sa["x0"], sa["params"], block=False)
+    pb = h2.solve_batch(sb["xinit"], sb["x0"], sb["params"], block=False)
+    with pytest.raises(SolverError):
+        h1.solve_batch(sb["xinit"], sb["x0"], sb["params"], block=False)
+    h1.wait(); h2.wait()
+    for r, p in ((ra, pa), (rb, pb)):
+        assert np.array_equal(r["z"], p["z"]) and np.array_equal(r["exitflag"], p["exitflag"])
+        assert np.array_equal(r["action"], p["action"]) and np.array_equal(r["obj"], p["obj"])
+    assert (ra["exitflag"] == 1).all()
+
+
+def test_options_roundtrip_and_iteration_bounds(built):
+    """rmpc_set_options / rmpc_get_options, max_iter and stall_window bound the work of a problem, bad values are refused."""
+    from robot_mpcs_b200.planner.solver import SolverError
+    sdir = "boxer_n3_01_H30_noSlack"
+    B = 512
+    s = sc.boxer_radial(_pm(sdir), B)
+    d = _to_dev(s)
+    solver = _solver(sdir, B)
+    o = solver.options()
+    assert o["max_iter"] == 200 and o["creep_trigger"] == 3 and o["stall_window"] == 0
+    full = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    solver.set_options(max_iter=30)
+    capped = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    assert int(capped["iters"].max()) <= 30
+    same = (full["iters"] <= 30).cpu().numpy()               # the convergence test of iteration 30 still runs
+    assert np.array_equal(full["z"].cpu().numpy()[same], capped["z"].cpu().numpy()[same])   # untouched problems: same bits
+    assert set(np.unique(capped["exitflag"].cpu().numpy()[~same]).tolist()) <= {0, -7}
+    solver.set_options(max_iter=200, stall_window=25)
+    st = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    ef = st["exitflag"].cpu().numpy()
+    assert (ef == 1).mean() > 0.9 and set(np.unique(ef).tolist()) <= {1, 0, -7}
+    conv = ef == 1
+    assert np.array_equal(st["z"].cpu().numpy()[conv], full["z"].cpu().numpy()[conv])
+    with pytest.raises(SolverError):
+        solver.set_options(stall_window=-1)
+    assert solver.options()["stall_window"] == 25          # a refused set leaves the handle's options as they were
+    solver.set_options(precision=1)                        # mixed precision is not in this build: refused at solve time
+    with pytest.raises(SolverError):
+        solver.solve_batch(d["xinit"], d["x0"], d["params"])
