@@ -90,6 +90,12 @@ template <> struct Group<32> {
   __device__ __forceinline__ double sum(double v) const { return warp_sum(v); }
   __device__ __forceinline__ double max(double v) const { return warp_max(v); }
   __device__ __forceinline__ double min(double v) const { return -warp_max(-v); }
+  __device__ __forceinline__ float max(float v) const {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+  }
+  __device__ __forceinline__ float min(float v) const { return -max(-v); }
   __device__ __forceinline__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
   __device__ __forceinline__ double bcast(double v, int src) const { return __shfl_sync(0xffffffffu, v, src); }
 };
@@ -186,7 +192,8 @@ struct Ipm {
   // ---- A: stage-parallel derivatives ----------------------------------------------------------
   RMPC_HD void derivs(const bool exact, const T reg, Red<T>& o) {
     LogAcc<T> lacc;
-    T f = T(0), theta = T(0), res_eq = T(0), cmin = T(1e300), cmax = T(0), msum = T(0), shmax = T(0), smin = T(1e300);
+    T f = T(0), theta = T(0), res_eq = T(0), msum = T(0), smin = T(1e300);
+    float cmin = 3e38f, cmax = 0.0f, shmax = 0.0f;  // only compared with tolerances: single precision is enough
     bool pole = false;
     RMPC_UNROLL
     for (int sl = 0; sl < SLOTS; ++sl) {
@@ -206,11 +213,16 @@ struct Ipm {
           y1[r] = trcp(sr);
           sig[r] = lr * y1[r];
           lacc.mul(sr);
-          cmax = tmax(cmax, sr * lr);
-          cmin = tmin(cmin, sr * lr);
+          const float cr = float(sr * lr);
+          cmax = fmaxf(cmax, cr);
+          cmin = fminf(cmin, cr);
           msum += lr;
-          shmax = tmax(shmax, T(sh[sl][r]));
-          if (sh[sl][r] > 0.0f) smin = tmin(smin, sr - T(1e-6f * sh[sl][r]));  // a slack this small next to its shift cannot recover  // slack of a row that is still shifted
+          shmax = fmaxf(shmax, sh[sl][r]);
+        }
+        if (shmax > 0.0f) {  // rows that started infeasible (rare): a slack this small next to its shift cannot recover
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r)
+            if (sh[sl][r] > 0.0f) smin = tmin(smin, s[sl][r] - T(1e-6f * sh[sl][r]));
         }
         RMPC_UNROLL
         for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lam[sl][M::geo_row(r)]; }
@@ -279,7 +291,7 @@ struct Ipm {
       }
     }
     o.f = g.sum(f); o.theta = g.sum(theta); o.logs = g.sum(lacc.value()); o.res_eq = g.max(res_eq);
-    o.comp_min = g.min(cmin); o.comp_max = g.max(cmax); o.mult_sum = g.sum(msum); o.shift_max = g.max(shmax); o.s_min = g.min(smin);
+    o.comp_min = T(g.min(cmin)); o.comp_max = T(g.max(cmax)); o.mult_sum = g.sum(msum); o.shift_max = T(g.max(shmax)); o.s_min = g.min(smin);
     o.pole = g.any(pole);
     g.sync();
   }
@@ -557,7 +569,8 @@ struct Ipm {
       // ---- Newton step, linear step-length estimates, merit slope
       rollout(mu);
       const T tau = tmax(T(opt.tau_min), T(1) - mu);
-      T rp = T(0), rd = T(0), dphi = T(0);
+      float rp = 0.0f, rd = 0.0f;  // step-length caps: single precision is enough (the true rows are checked in the line search)
+      T dphi = T(0);
       RMPC_UNROLL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
@@ -572,14 +585,14 @@ struct Ipm {
             const T dsr = gd[r];
             const T rs = trcp(sr);
             const T dlr = mu * rs - lr - (lr * rs) * dsr;
-            rp = tmax(rp, -dsr * rs);            // largest relative decrease of a slack ...
-            rd = tmax(rd, -dlr * trcp(lr));      // ... and of a multiplier, for the fraction-to-boundary rule
+            rp = fmaxf(rp, float(-dsr * rs));             // largest relative decrease of a slack ...
+            rd = fmaxf(rd, -float(dlr) / float(lr));      // ... and of a multiplier, for the fraction-to-boundary rule
             dphi -= mu * dsr * rs;
           }
         }
       }
       rp = g.max(rp); rd = g.max(rd); dphi = g.sum(dphi);
-      const T ap = rp > tau ? tau * trcp(rp) : T(1), ad = rd > tau ? tau * trcp(rd) : T(1);
+      const T ap = T(rp) > tau ? tau / T(rp) : T(1), ad = T(rd) > tau ? tau / T(rd) : T(1);
       if (so.theta > T(1e-14)) {
         const T need = dphi * trcp(T(0.9) * so.theta);
         if (need > rho_pen) rho_pen = need * T(1.1) + T(1e-3);

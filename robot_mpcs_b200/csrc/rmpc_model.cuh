@@ -42,20 +42,23 @@ RMPC_HD float trsqrt(float a) { return 1.0f / sqrtf(a); }
 RMPC_HD void tsincos(float a, float* s, float* c) { *s = sinf(a); *c = cosf(a); }
 #if defined(__CUDA_ARCH__)
 // Device: the libm expansions of sincos / log are ~150 / ~60 instructions each; one out-of-line copy keeps the solve
-// kernel inside the instruction cache.  Reciprocal and reciprocal square root: float seed + Newton steps in double
-// (full double accuracy to a few ulp for the magnitudes met here, 1e-30 .. 1e30), instead of the IEEE division /
-// square-root sequences with their slow-path branches.
+// kernel inside the instruction cache.  Reciprocal and reciprocal square root: the 64-bit MUFU seed (rcp/rsqrt
+// .approx.ftz.f64, about 20 bits, one instruction, no conversions) + two Newton steps in double: a few ulp
+// (tests/test_gpu_parity.py::test_device_reciprocals) instead of the IEEE division / square-root sequences with
+// their slow-path branches.  Arguments are positive normal numbers here.
 __device__ __noinline__ void tsincos(double a, double* s, double* c) { sincos(a, s, c); }
 __device__ __noinline__ double tlog(double a) { return log(a); }
 __device__ __forceinline__ double trcp(double a) {
-  double r = double(__frcp_rn(float(a)));
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
   r = r * (2.0 - a * r);
   r = r * (2.0 - a * r);
   return r;
 }
 __device__ __forceinline__ double trsqrt(double a) {
-  double r = double(rsqrtf(float(a)));
-  const double ha = 0.5 * a;  // seed: 22 bits; two Newton steps: 43, then > 53 bits
+  double r;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+  const double ha = 0.5 * a;
   r = r * (1.5 - ha * r * r);
   r = r * (1.5 - ha * r * r);
   return r;
@@ -73,20 +76,20 @@ template <> struct LogAcc<double> {
   double m;
   int e;
   RMPC_HD LogAcc() : m(1.0), e(0) {}
-  RMPC_HD void mul(double x) {  // x > 0, normal
+  // x > 0, normal.  Every factor is a mantissa in [0.5, 1): up to ~1000 of them stay clear of underflow (callers
+  // multiply NH * SLOTS < 100 values).
+  RMPC_HD void mul(double x) {
 #if defined(__CUDA_ARCH__)
-    const long long b = __double_as_longlong(x);
-    e += int((b >> 52) & 0x7ff) - 1022;
-    m *= __longlong_as_double((b & 0x800fffffffffffffLL) | 0x3fe0000000000000LL);
+    const int hi = __double2hiint(x);
+    e += ((hi >> 20) & 0x7ff) - 1022;
+    m *= __hiloint2double((hi & 0x800fffff) | 0x3fe00000, __double2loint(x));
 #else
     int ex;
     m *= frexp(x, &ex);
     e += ex;
 #endif
-    if (m < 1e-200) { m *= 1e200; lg += -460.51701859880916; }  // ln(1e-200): keeps long products normal
   }
-  double lg = 0.0;
-  RMPC_HD double value() const { return tlog(m) + 0.6931471805599453 * double(e) + lg; }
+  RMPC_HD double value() const { return tlog(m) + 0.6931471805599453 * double(e); }
 };
 template <> struct LogAcc<float> {
   float a;

@@ -234,3 +234,21 @@ def test_options_roundtrip_and_iteration_bounds(built):
     solver.set_options(precision=1)                        # mixed precision is not in this build: refused at solve time
     with pytest.raises(SolverError):
         solver.solve_batch(d["xinit"], d["x0"], d["params"])
+
+
+def test_device_reciprocals(built):
+    """trcp / trsqrt of csrc/rmpc_model.cuh (MUFU seed + two Newton steps) against IEEE division / sqrt: a few ulp over
+    the magnitudes the solver meets (slacks down to 1e-13, barrier weights up to 1e15)."""
+    import ctypes
+    import torch
+    lib = ctypes.CDLL(os.path.join(SOLVERS, "libpeak_fma.so"))
+    lib.recip_launch.argtypes = [ctypes.c_int] + [ctypes.c_void_p] * 4
+    g = torch.Generator(device="cuda:0").manual_seed(5)
+    n = 1 << 20
+    x = torch.exp(torch.rand(n, dtype=torch.float64, device="cuda:0", generator=g) * 140.0 - 70.0)   # 4e-31 .. 2.5e30
+    rcp, rsq = torch.empty_like(x), torch.empty_like(x)
+    assert lib.recip_launch(n, x.data_ptr(), rcp.data_ptr(), rsq.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert float(((rcp * x) - 1).abs().max()) < 1e-15
+    assert float((rcp / (1.0 / x) - 1).abs().max()) < 1e-15
+    assert float((rsq / torch.rsqrt(x) - 1).abs().max()) < 1e-15
