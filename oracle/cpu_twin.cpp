@@ -69,6 +69,7 @@ int twin_solve_batch(int B, const double* xinit, const double* x0, const double*
 }
 
 // model-function probes for the derivative / FK parity tests
+void twin_sincos(int n, const double* x, double* s, double* c) { for (int i = 0; i < n; ++i) rmpc::tsincos(x[i], s + i, c + i); }
 void twin_stage_values(const double* z, const double* p, double* f, double* h) {
   rmpc::StageVal<M, double> sv;
   rmpc::stage_values<M, double>(z, p, sv);

@@ -84,17 +84,18 @@ __device__ __noinline__ double warp_max(double v) {
   for (int o = 16; o > 0; o >>= 1) { const double w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
   return v;
 }
+__device__ __noinline__ float warp_maxf(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
 template <> struct Group<32> {
   int lane;
   __device__ __forceinline__ void sync() const { __syncwarp(); }
   __device__ __forceinline__ double sum(double v) const { return warp_sum(v); }
   __device__ __forceinline__ double max(double v) const { return warp_max(v); }
   __device__ __forceinline__ double min(double v) const { return -warp_max(-v); }
-  __device__ __forceinline__ float max(float v) const {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-    return v;
-  }
+  __device__ __forceinline__ float max(float v) const { return warp_maxf(v); }
   __device__ __forceinline__ float min(float v) const { return -max(-v); }
   __device__ __forceinline__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
   __device__ __forceinline__ double bcast(double v, int src) const { return __shfl_sync(0xffffffffu, v, src); }
@@ -586,7 +587,7 @@ struct Ipm {
             const T rs = trcp(sr);
             const T dlr = mu * rs - lr - (lr * rs) * dsr;
             rp = fmaxf(rp, float(-dsr * rs));             // largest relative decrease of a slack ...
-            rd = fmaxf(rd, -float(dlr) / float(lr));      // ... and of a multiplier, for the fraction-to-boundary rule
+            rd = fmaxf(rd, fdiv_approx(-float(dlr), float(lr)));      // ... and of a multiplier, for the fraction-to-boundary rule
             dphi -= mu * dsr * rs;
           }
         }

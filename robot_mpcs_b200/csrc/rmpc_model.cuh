@@ -34,6 +34,13 @@ template <class T> RMPC_HD T tmax(T a, T b) { return a > b ? a : b; }
 template <class T> RMPC_HD T tmin(T a, T b) { return a < b ? a : b; }
 RMPC_HD float tabs(float a) { return fabsf(a); }
 RMPC_HD double tabs(double a) { return fabs(a); }
+RMPC_HD float fdiv_approx(float a, float b) {  // 2 ulp: for ratios that only cap a step length
+#if defined(__CUDA_ARCH__)
+  return __fdividef(a, b);
+#else
+  return a / b;
+#endif
+}
 RMPC_HD float tsqrt(float a) { return sqrtf(a); }
 RMPC_HD double tsqrt(double a) { return sqrt(a); }
 RMPC_HD float tlog(float a) { return logf(a); }
@@ -46,7 +53,7 @@ RMPC_HD void tsincos(float a, float* s, float* c) { *s = sinf(a); *c = cosf(a); 
 // .approx.ftz.f64, about 20 bits, one instruction, no conversions) + two Newton steps in double: a few ulp
 // (tests/test_gpu_parity.py::test_device_reciprocals) instead of the IEEE division / square-root sequences with
 // their slow-path branches.  Arguments are positive normal numbers here.
-__device__ __noinline__ void tsincos(double a, double* s, double* c) { sincos(a, s, c); }
+__device__ __noinline__ void tsincos_lib(double a, double* s, double* c) { sincos(a, s, c); }
 __device__ __noinline__ double tlog(double a) { return log(a); }
 __device__ __forceinline__ double trcp(double a) {
   double r;
@@ -64,11 +71,55 @@ __device__ __forceinline__ double trsqrt(double a) {
   return r;
 }
 #else
-RMPC_HD void tsincos(double a, double* s, double* c) { *s = sin(a); *c = cos(a); }
+RMPC_HD void tsincos_lib(double a, double* s, double* c) { *s = sin(a); *c = cos(a); }
 RMPC_HD double tlog(double a) { return log(a); }
 RMPC_HD double trcp(double a) { return 1.0 / a; }
 RMPC_HD double trsqrt(double a) { return 1.0 / sqrt(a); }
 #endif
+
+// sin and cos together: Cody-Waite reduction by pi/2 in two pieces (exact for |x| < 1e5) and the fdlibm kernel
+// polynomials on [-pi/4, pi/4]; ~35 instructions against ~90 plus a call for the library routine, which remains the
+// path for huge arguments.  Accuracy ~1 ulp of the result's scale (tests/test_oracle_model.py::test_fast_sincos).
+#if defined(__CUDA_ARCH__)
+__device__ __noinline__   // one copy: the solve kernel is instruction-cache bound (inlined at its 12 call sites it ran 7-18 % slower)
+#else
+RMPC_HD
+#endif
+void tsincos(double x, double* sn, double* cs) {
+  if (!(tabs(x) < 1e5)) { tsincos_lib(x, sn, cs); return; }
+  const double magic = 6755399441055744.0;  // 1.5 * 2^52: adding it rounds to the nearest integer
+  const double t = x * 0.63661977236758134308 + magic;
+  const double kd = t - magic;
+#if defined(__CUDA_ARCH__)
+  const int q = __double2loint(t);
+  double r = __fma_rn(-kd, 1.57079632673412561417e+00, x);
+  r = __fma_rn(-kd, 6.07710050650619224932e-11, r);
+#else
+  long long tb;
+  __builtin_memcpy(&tb, &t, 8);
+  const int q = int(tb & 0xffffffffLL);
+  double r = __builtin_fma(-kd, 1.57079632673412561417e+00, x);
+  r = __builtin_fma(-kd, 6.07710050650619224932e-11, r);
+#endif
+  const double z = r * r;
+  double ps = 1.58969099521155010221e-10;
+  ps = ps * z + -2.50507602534068634195e-08;
+  ps = ps * z + 2.75573137070700676789e-06;
+  ps = ps * z + -1.98412698298579493134e-04;
+  ps = ps * z + 8.33333333332248946124e-03;
+  ps = ps * z + -1.66666666666666324348e-01;
+  const double sr = r + (r * z) * ps;
+  double pc = -1.13596475577881948265e-11;
+  pc = pc * z + 2.08757232129817482790e-09;
+  pc = pc * z + -2.75573143513906633035e-07;
+  pc = pc * z + 2.48015872894767294178e-05;
+  pc = pc * z + -1.38888888888741095749e-03;
+  pc = pc * z + 4.16666666666666019037e-02;
+  const double cr = (1.0 - 0.5 * z) + (z * z) * pc;
+  const double a = (q & 1) ? cr : sr, b = (q & 1) ? sr : cr;
+  *sn = (q & 2) ? -a : a;
+  *cs = ((q + 1) & 2) ? -b : b;
+}
 
 // sum_i log(x_i) as log(prod mantissas) + ln2 * sum exponents: one log per stage instead of one per row.
 template <class T> struct LogAcc;

@@ -172,3 +172,18 @@ def test_model_derivatives_match_autograd(built, cfg):
         nut = torch.tensor(nu, dtype=DT)
         Q_ref = torch.autograd.functional.hessian(lambda v: (nut * m.step(v[: m.nx], v[m.nx:])).sum(), zt).numpy()
         assert np.allclose(Q, Q_ref, rtol=1e-9, atol=1e-11)
+
+
+def test_fast_sincos():
+    """The inline sincos of csrc/rmpc_model.cuh (same source on host and device) against libm over the fast-path range,
+    at quadrant boundaries, and on the library fallback for huge arguments."""
+    import ctypes
+    from oracle.build_twin import Twin
+    tw = Twin(os.path.join(SOLVERS, "boxer_n3_01_H30_noSlack"))
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.uniform(-10, 10, 200000), rng.uniform(-1e5, 1e5, 200000), np.arange(-64, 65) * (np.pi / 4),
+                        np.arange(-64, 65) * (np.pi / 4) + 1e-9, [0.0, 1e-300, -1e-8, 1e7, -3e9]])
+    s, c = np.empty_like(x), np.empty_like(x)
+    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    tw.lib.twin_sincos(len(x), p(x), p(s), p(c))
+    assert np.abs(s - np.sin(x)).max() < 4e-16 and np.abs(c - np.cos(x)).max() < 4e-16
