@@ -101,6 +101,18 @@ int rmpc_set_params(rmpc_solver* s, int B, double* params, const int* idx, int n
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py reports it). */
 long rmpc_launch_count(void);
 
+/* Batched free-space decomposition (robotmpcs/utils/free_space_decomposition.py:61-116 as driven by
+ * examples/boxer_example.py:132-148,191-203): for every problem b and stage k the seed is the lidar position of the
+ * reference state ref[b*ref_batch_stride + k*ref_stage_stride + {0,1,2}] = (x, y, theta), i.e. (x, y) + Rot(theta)
+ * (lidar_offset, 0) at height lidar_z; up to K half-planes [n0 n1 n2 c] are grown greedily from the nearest points of
+ * points[b][n_points][3] within max_radius, unused slots get the reference's dummy plane.  Results go to
+ * out[b][k][K][4] (may be NULL) and/or into params[b][k][idx[c] .. idx[c]+3] (may be NULL; idx is a HOST array of the K
+ * `lin_constrs_c` parameter indices).  ref may point into a previous plan z (strides N*nvar, nvar) or at one state per
+ * problem (strides 3, 0).  Device pointers, asynchronous on `stream`.  K <= 16, n_points <= 128. */
+int rmpc_fsd_constraints(rmpc_solver* s, int B, const double* points, int n_points, const double* ref, long ref_batch_stride,
+                         long ref_stage_stride, double max_radius, double lidar_offset, double lidar_z, int K, double* out,
+                         double* params, const int* idx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

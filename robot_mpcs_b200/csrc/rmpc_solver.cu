@@ -13,6 +13,7 @@
 
 #include "model_traits.h"
 #include "rmpc_ipm.cuh"
+#include "rmpc_fsd.cuh"
 #include "rmpc.h"
 
 using M = ModelTraits;
@@ -365,6 +366,33 @@ int rmpc_set_params(rmpc_solver* s, int B, double* params, const int* idx, int n
   CK(cudaMemcpyAsync(s->d_idx, idx, sizeof(int) * n_idx, cudaMemcpyHostToDevice, st));
   const long total = (long)B * M::N * n_idx;
   scatter_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(B, n_idx, stage_varying, s->d_idx, values, params);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int rmpc_fsd_constraints(rmpc_solver* s, int B, const double* points, int n_points, const double* ref, long ref_batch_stride,
+                         long ref_stage_stride, double max_radius, double lidar_offset, double lidar_z, int K, double* out,
+                         double* params, const int* idx, void* stream) {
+  if (!s || !points || !ref || B <= 0 || (!out && !params)) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  if (K <= 0 || K > kFsdMaxK || n_points <= 0 || n_points > kFsdMaxPoints) {
+    snprintf(g_err, sizeof g_err, "K must be in [1, %d] and n_points in [1, %d]", kFsdMaxK, kFsdMaxPoints);
+    return -1;
+  }
+  FsdArgs a;
+  memset(&a, 0, sizeof a);
+  a.B = B; a.N = M::N; a.P = n_points; a.K = K; a.points = points; a.ref = ref; a.ref_bs = ref_batch_stride; a.ref_ss = ref_stage_stride;
+  a.max_radius = max_radius; a.lidar_offset = lidar_offset; a.lidar_z = lidar_z; a.out = out; a.params = params; a.npar = M::NPAR;
+  if (params) {
+    if (!idx) { snprintf(g_err, sizeof g_err, "idx is required with params"); return -1; }
+    for (int c = 0; c < K; ++c) {
+      if (idx[c] < 0 || idx[c] + 4 > M::NPAR) { snprintf(g_err, sizeof g_err, "parameter index %d out of range", idx[c]); return -1; }
+      a.idx[c] = idx[c];
+    }
+  }
+  CK(cudaSetDevice(s->device));
+  const long warps = (long)B * M::N;
+  fsd_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, (cudaStream_t)stream>>>(a);
   g_launches++;
   CK(cudaGetLastError());
   return 0;

@@ -40,7 +40,7 @@ class RmpcInfo(ctypes.Structure):
 
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
-           "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_shift_horizon",
+           "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
            "rmpc_set_params", "rmpc_launch_count"]
 
 
@@ -70,6 +70,9 @@ def load_library(solver_dir: str) -> ctypes.CDLL:
     lib.rmpc_shift_horizon.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.rmpc_set_params.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_int,
                                     ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    lib.rmpc_fsd_constraints.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
+                                         ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_int,
+                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_void_p]
     lib.rmpc_launch_count.restype = ctypes.c_long
     return lib
 
@@ -233,3 +236,29 @@ class Solver:
                                     ctypes.c_void_p(stream)) != 0:
             raise SolverError(self._err())
         return params
+
+    def fsd_constraints(self, points, ref, K, max_radius=5.0, params=None, idx=None, want_out=True, lidar_offset=0.4, lidar_z=0.02):
+        """Batched free-space decomposition on the device (robotmpcs/utils/free_space_decomposition.py as driven by
+        examples/boxer_example.py:132-148,191-203).  points[B,P,3] (CUDA, float64); ref[B,N,>=3] (e.g. the previous plan
+        z[B,N,nvar]) or ref[B,>=3] (one state per problem, used for every stage).  Returns [B,N,K,4] and/or writes the planes
+        into params[B,N,npar] at the `lin_constrs_c` indices idx[c]."""
+        B, P = points.shape[0], points.shape[1]
+        points = points.to(torch.float64).contiguous()
+        ref = ref.to(torch.float64)
+        if ref.stride(-1) != 1:
+            ref = ref.contiguous()
+        if ref.dim() == 2:
+            bs, ss = ref.stride(0), 0
+        else:
+            if ref.shape[1] != self.N:
+                raise SolverError(f"ref has {ref.shape[1]} stages, the solver {self.N}")
+            bs, ss = ref.stride(0), ref.stride(1)
+        out = torch.empty(B, self.N, K, 4, dtype=torch.float64, device=points.device) if want_out else None
+        idx_arr = (ctypes.c_int * K)(*[int(i) for i in idx]) if idx is not None else None
+        stream = torch.cuda.current_stream(points.device).cuda_stream
+        rc = self.lib.rmpc_fsd_constraints(self._h, B, points.data_ptr(), P, ref.data_ptr(), bs, ss, max_radius, lidar_offset, lidar_z,
+                                           K, out.data_ptr() if want_out else None, params.data_ptr() if params is not None else None,
+                                           idx_arr, ctypes.c_void_p(stream))
+        if rc != 0:
+            raise SolverError("rmpc_fsd_constraints failed: " + self._err())
+        return out

@@ -184,3 +184,23 @@ def panda(pmap, B, N=20, npar=50, seed=1, jitter=True):
     x0 = np.zeros((B, N, 21))
     x0[:, :, :14] = xinit[:, None, :]
     return {"xinit": xinit, "x0": x0, "params": P}
+
+
+def lidar_scene(B, N, P=64, seed=0):
+    """Synthetic input of the free-space decomposition (stands in for urdfenvs' Lidar sensor, boxer_example.py:153-161,
+    which is unavailable here): per problem a robot pose, N reference states along a gently curving path from it, and
+    P lidar returns at `range_i` along P equally spaced rays from the lidar position (range ~ U(0.3, 6), so some fall
+    outside max_radius = 5), at the lidar height 0.02.  Returns points[B,P,3] (absolute) and ref[B,N,3] = (x, y, theta)."""
+    g = np.random.default_rng(seed)
+    x0 = g.uniform(-1, 1, (B, 2))
+    th0 = g.uniform(-math.pi, math.pi, B)
+    v = g.uniform(0.0, 0.5, B)
+    om = g.uniform(-0.5, 0.5, B)
+    t = np.arange(N)[None, :] * 0.1
+    th = th0[:, None] + om[:, None] * t
+    ref = np.stack([x0[:, 0:1] + v[:, None] * t * np.cos(th), x0[:, 1:2] + v[:, None] * t * np.sin(th), th], axis=2)
+    ang = th0[:, None] + np.arange(P)[None, :] * (2 * math.pi / P)
+    rng_ = g.uniform(0.3, 6.0, (B, P))
+    lp = x0 + 0.4 * np.stack([np.cos(th0), np.sin(th0)], axis=1)
+    pts = np.stack([lp[:, 0:1] + rng_ * np.cos(ang), lp[:, 1:2] + rng_ * np.sin(ang), np.full((B, P), 0.02)], axis=2)
+    return np.ascontiguousarray(pts), np.ascontiguousarray(ref)
