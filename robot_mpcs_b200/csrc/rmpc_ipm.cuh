@@ -42,6 +42,7 @@ struct Options {
   double kappa;        // multipliers are kept above mu/(kappa s)
   double tau_min;      // fraction-to-boundary parameter tau = max(tau_min, 1 - mu)
   double lm0, lm_up, lm_down, lm_trigger;  // adaptive damping: start value, growth, decay, backtracks that trigger growth
+  double gn_hold_max;                       // longest run of iterations that skip the exact-Hessian attempt after it failed (0: always try)
   double stall_window;                      // give up (-7) when the optimality error has not dropped 10x within this many iterations (0 = never)
   double creep_trigger, creep_factor;      // consecutive boundary-cut full steps that trigger a barrier increase, and its factor
 };
@@ -50,7 +51,7 @@ RMPC_HD Options default_options() {
   Options o;
   o.max_iter = 200; o.hessian = 1;
   o.tol_stat = 1e-6; o.tol_eq = 1e-8; o.tol_ineq = 1e-8; o.tol_comp = 1e-8;
-  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3; o.creep_trigger = 3; o.creep_factor = 10; o.stall_window = 0;
+  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3; o.creep_trigger = 3; o.creep_factor = 10; o.stall_window = 0; o.gn_hold_max = 4;
   return o;
 }
 
@@ -527,18 +528,22 @@ struct Ipm {
     Red<T> so;
     so.f = so.res_stat = so.res_eq = so.comp_max = so.shift_max = T(0);
     T rho_pen = T(1);
-    int ncreep = 0, it_ref = 0;
+    int ncreep = 0, it_ref = 0, gn_hold = 0, gn_len = 1;
     T err_ref = T(1e300);
     T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
     if (g.any(pole0)) { info.exitflag = -8; it = opt.max_iter + 1; }
     for (; it <= opt.max_iter; ++it) {
-      bool exact = opt.hessian == 1;
+      // An indefinite exact Hessian costs a whole derivative pass + sweep before the Gauss-Newton retry, and far from
+      // the solution it is indefinite iteration after iteration: after a failure the exact attempt is skipped for
+      // 1, 2, 4, 4, ... iterations (gn_hold), until it succeeds again.
+      bool exact = opt.hessian == 1 && gn_hold == 0;
+      if (gn_hold > 0) --gn_hold;
       T reg = T(opt.reg) + lm;
       for (int tries = 0; tries < 5; ++tries) {
         derivs(exact, reg, so);
         sweep(so);
-        if (so.ok) break;
-        if (exact) exact = false;                       // not positive definite: Gauss-Newton
+        if (so.ok) { if (exact) gn_len = 1; break; }
+        if (exact) { exact = false; gn_hold = gn_len; gn_len = gn_len < int(opt.gn_hold_max) ? 2 * gn_len : gn_len; }  // not positive definite: Gauss-Newton
         else reg = tmax(reg * T(100), T(1e-6));         // rounding broke it (huge barrier weights): Levenberg
       }
       if (!so.finite || !so.ok) { info.exitflag = so.ok ? -6 : -5; break; }
