@@ -305,6 +305,9 @@ struct Ipm {
     constexpr int LDF = Dims<M>::LDF, NQD = Dims<M>::NQD;
     T res_stat = T(0), nsum = T(0);
     bool ok = true;
+    int fxx[NX];  // warp: where the lane that owns row i of P finds F(i, j) in the lower triangle (stage-invariant)
+    RMPC_UNROLL
+    for (int j = 0; j < NX; ++j) { const int i = g.lane < NX ? g.lane : 0; fxx[j] = i >= j ? i * LDF + j : j * LDF + i; }
     for (int k = N - 1; k >= 0; --k) {
       StageShared<M, T>& st = S.st[k];
       const bool dyn = k < N - 1;
@@ -396,7 +399,7 @@ struct Ipm {
         T Pi[NX];
         RMPC_UNROLL
         for (int j = 0; j < NX; ++j) {
-          T v = S.F[i >= j ? i * LDF + j : j * LDF + i];  // Fxx from its lower triangle
+          T v = (G > 1) ? S.F[fxx[j]] : S.F[i >= j ? i * LDF + j : j * LDF + i];  // Fxx from its lower triangle
           RMPC_UNROLL
           for (int l = 0; l < NU; ++l) v += fu[l] * st.K(l, j);
           Pi[j] = v;
