@@ -72,6 +72,7 @@ template <> struct Group<1> {
   template <class T> RMPC_HD T min(T v) const { return v; }
   RMPC_HD bool any(bool p) const { return p; }
   template <class T> RMPC_HD T bcast(T v, int) const { return v; }
+  RMPC_HD void align() const {}
 };
 #if defined(__CUDACC__)
 // double reductions out of line: ~20 call sites x 15 instructions otherwise
@@ -100,6 +101,15 @@ template <> struct Group<32> {
   __device__ __forceinline__ float min(float v) const { return -max(-v); }
   __device__ __forceinline__ bool any(bool p) const { return __any_sync(0xffffffffu, p) != 0; }
   __device__ __forceinline__ double bcast(double v, int src) const { return __shfl_sync(0xffffffffu, v, src); }
+  // Block-wide rendezvous at the top of every solver iteration: the warps of a block (one problem each) then walk
+  // through the same code at about the same time, so one instruction-cache fill serves all of them (the kernel's
+  // L1.5 instruction-request rate is at 89 % of peak).  Off by default: see RMPC_WARPS_FIXED in rmpc_solver.cu.  A warp
+  // without work keeps answering with 1 until every warp does.
+  __device__ __forceinline__ void align() const {
+#if RMPC_WARPS > 1
+    __syncthreads_and(0);
+#endif
+  }
 };
 #endif
 
@@ -536,6 +546,7 @@ struct Ipm {
     T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
     if (g.any(pole0)) { info.exitflag = -8; it = opt.max_iter + 1; }
     for (; it <= opt.max_iter; ++it) {
+      g.align();
       // An indefinite exact Hessian costs a whole derivative pass + sweep before the Gauss-Newton retry, and far from
       // the solution it is indefinite iteration after iteration: after a failure the exact attempt is skipped for
       // 1, 2, 4, 4, ... iterations (gn_hold), until it succeeds again.

@@ -9,19 +9,20 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <atomic>
 
 #include "model_traits.h"
+#ifndef RMPC_WARPS_FIXED
+#define RMPC_WARPS_FIXED 1
+#endif
+#define RMPC_WARPS RMPC_WARPS_FIXED
 #include "rmpc_ipm.cuh"
 #include "rmpc_fsd.cuh"
 #include "rmpc.h"
 
 using M = ModelTraits;
 using namespace rmpc;
-
-#ifndef RMPC_WARPS
-#define RMPC_WARPS 1   // warps (= problems in flight) per thread block
-#endif
 
 static thread_local char g_err[512] = "";
 static std::atomic<long> g_launches{0};
@@ -64,11 +65,20 @@ struct rmpc_solver {
 // written in the reference's own layout ([B][N][nvar], [B][N][npar]); there is no separate pack/unpack pass.
 using Shared = ProblemShared<M, double>;
 constexpr size_t kSharedPerWarp = (sizeof(Shared) + 15) / 16 * 16;
+// Warps (= problems) per thread block.  With more than one, the warps of a block meet at the top of every solver
+// iteration (Group<32>::align) so that they walk through the same code together and share instruction-cache fills.
+// Measured on B200 (boxer, 20 steps): 1 warp/block 702 k solves/s, 2: 622 k, 3: 574 k, 7: 534 k — waiting for the
+// slowest iteration of the block costs more than the shared fetches save, so the default stays at 1.
+#ifndef RMPC_WARPS_FIXED
+#define RMPC_WARPS_FIXED 1
+#endif
+constexpr int kWarps = RMPC_WARPS_FIXED;
+static_assert(kWarps >= 1, "one problem does not fit into the shared memory of an SM");
 
 #ifndef RMPC_MIN_BLOCKS
 #define RMPC_MIN_BLOCKS 1   // resident blocks per SM the register allocation must allow
 #endif
-__global__ void __launch_bounds__(32 * RMPC_WARPS, RMPC_MIN_BLOCKS)
+__global__ void __launch_bounds__(32 * kWarps, RMPC_MIN_BLOCKS)
 solve_kernel(int B, const double* __restrict__ xinit, const double* __restrict__ x0, const double* __restrict__ params,
              double* __restrict__ z_out, double* __restrict__ action, rmpc_info info, Options opt, int control_mode,
              int* __restrict__ counter) {
@@ -80,7 +90,11 @@ solve_kernel(int B, const double* __restrict__ xinit, const double* __restrict__
     int b = 0;
     if (g.lane == 0) b = atomicAdd(counter, 1);
     b = __shfl_sync(0xffffffffu, b, 0);
-    if (b >= B) break;
+    if (b >= B) {
+      // out of work: keep meeting the other warps of the block at their iteration rendezvous until all are out of work
+      if (kWarps > 1) while (!__syncthreads_and(1)) {}
+      break;
+    }
     const ParamView<double> pv{params + (size_t)b * M::N * M::NPAR, M::NPAR, 1};
     Info inf;
     {
@@ -194,11 +208,15 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   };
   if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
   if ((e = cudaMalloc(&s->counter, sizeof(int) * kCounterSlots)) != cudaSuccess) return fail("cudaMalloc", e);
-  const size_t smem = kSharedPerWarp * RMPC_WARPS;
+  const size_t smem = kSharedPerWarp * kWarps;
   if ((e = cudaFuncSetAttribute(solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
     return fail("cudaFuncSetAttribute(shared memory)", e);
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel, 32 * RMPC_WARPS, smem)) != cudaSuccess)
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel, 32 * kWarps, smem)) != cudaSuccess)
     return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor", e);
+  if (const char* cap = getenv("RMPC_MAX_BLOCKS_PER_SM")) {  // experiment knob: fewer problems in flight per SM
+    const int c = atoi(cap);
+    if (c > 0 && c < s->blocks_per_sm) s->blocks_per_sm = c;
+  }
   if (s->blocks_per_sm < 1) { snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem); free_all(s); delete s; return nullptr; }
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
@@ -247,9 +265,9 @@ int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x
   const Options c = to_core(s->opt);
   // persistent grid: as many blocks as fit at once, never more than the problems need
   long grid = (long)s->blocks_per_sm * s->sm_count;
-  const long need = ((long)B + RMPC_WARPS - 1) / RMPC_WARPS;
+  const long need = ((long)B + kWarps - 1) / kWarps;
   if (grid > need) grid = need;
-  solve_kernel<<<(unsigned)grid, 32 * RMPC_WARPS, kSharedPerWarp * RMPC_WARPS, st>>>(B, xinit, x0, params, z_out, action_out, inf, c,
+  solve_kernel<<<(unsigned)grid, 32 * kWarps, kSharedPerWarp * kWarps, st>>>(B, xinit, x0, params, z_out, action_out, inf, c,
                                                                                    s->opt.control_mode, counter);
   g_launches++;
   CK(cudaGetLastError());
