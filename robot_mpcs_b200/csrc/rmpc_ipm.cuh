@@ -195,6 +195,7 @@ struct Ipm {
 
   // per-lane state of the stages this lane owns
   T lam[SLOTS][NH], s[SLOTS][NH];
+  bool any_shift[SLOTS];
   float sh[SLOTS][NH];  // shifts of the rows that started infeasible (any positive number works: single precision is enough)
   T Gg[SLOTS][NGEO1][NQ];
 
@@ -520,6 +521,7 @@ struct Ipm {
     RMPC_UNROLL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
+      any_shift[sl] = false;
       if (k < N) {
         T p[M::NPAR];
         load_params<M, T>(pv, k, p);
@@ -531,6 +533,7 @@ struct Ipm {
           const T hv = sv.h[r];
           const float shift = hv >= T(opt.delta) ? 0.0f : float(T(opt.delta) - hv);
           sh[sl][r] = shift;
+          any_shift[sl] = any_shift[sl] || shift > 0.0f;
           s[sl][r] = hv + T(shift);
           lam[sl][r] = mu * trcp(hv + T(shift));
         }
@@ -578,11 +581,14 @@ struct Ipm {
       }
       // ---- monotone barrier update (Fiacco-McCormick as in IPOPT): shrink mu while the current barrier
       //      problem is solved to within kappa_eps * mu
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
       for (int rep = 0; rep < 8; ++rep) {
         const T cmu = tmax(so.comp_max - mu, mu - so.comp_min);
         const T emu = tmax(tmax(so.res_stat, cmu) * isd, tmax(so.res_eq, so.shift_max));
         if (emu <= T(10) * mu && mu > T(opt.mu_min)) {
-          const T m15 = mu * tsqrt(mu);
+          const T m15 = mu * mu * trsqrt(mu);  // mu^1.5
           mu = tmax(T(opt.mu_min), tmin(T(0.2) * mu, m15));
         } else break;
       }
@@ -694,18 +700,30 @@ struct Ipm {
         if (k < N) {
           T gd[NH];
           row_dirs(sl, k, gd);
+          T snv[NH];  // new slacks: the row values of the accepted trial ...
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r) snv[r] = S.st[k].Qs[r];
+          if (any_shift[sl]) {  // ... plus, for rows that started infeasible (rare), a shift that shrinks while keeping s >= s/2
+            bool left = false;
+            RMPC_UNROLL
+            for (int r = 0; r < NH; ++r) {
+              const T sho = T(sh[sl][r]);
+              if (sho > T(0)) {
+                const T sn = snv[r] + sho;
+                const float shn = float(tmax(T(0), sho - T(0.5) * sn));
+                snv[r] = sn - (sho - T(shn));
+                sh[sl][r] = shn;
+                left = left || shn > 0.0f;
+              }
+            }
+            any_shift[sl] = left;
+          }
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];
             const T rs = trcp(sr);
             const T dlr = mu * rs - lr - (lr * rs) * gd[r];
-            const T sho = T(sh[sl][r]);
-            T sn = S.st[k].Qs[r] + sho;
-            if (sho > T(0)) {  // shrink the shift of a row that started infeasible, keeping s >= s/2
-              const float shn = float(tmax(T(0), sho - T(0.5) * sn));
-              sn -= sho - T(shn);
-              sh[sl][r] = shn;
-            }
+            const T sn = snv[r];
             T ln = lr + adu * dlr;
             const T mus = mu * trcp(sn);
             ln = tmin(tmax(ln, mus * ikappa), T(1e10) * mus);

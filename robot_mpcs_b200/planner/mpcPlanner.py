@@ -281,6 +281,7 @@ class MPCPlanner(object):
         ob = cat(args[:3], -1)
         if self._actionCounter >= self._config.interval:
             self._action, self._last_output, _info, self._last_flag = self.solve(ob)
+            self._last_iters = _info["iters"]
             self._actionCounter = 1
         else:
             self._actionCounter += 1

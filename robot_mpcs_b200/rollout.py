@@ -1,0 +1,83 @@
+"""Headless, device-resident closed-loop rollout of B scenarios: the stand-in for the reference's
+pybullet demos (examples/pointRobot_example.py:81-89, boxer_example.py:176-224 — the simulator and its GUI are
+unavailable on this box).  Per control step and for the whole batch: measured state -> MPCPlanner.computeAction (warm
+start, batched solve on the GPU) -> the first action drives the plant -> goal check.  The plant is the MPC's own
+discrete model (double integrator, or diff-drive with explicit-midpoint substeps), integrated here in torch on the
+device; nothing leaves the GPU until the summary at the end.
+
+    reference                                                   here
+    env.step(action) (pybullet)                                  plant_step(x, u)            (model = plant)
+    check_goal_reaching, boxer_example.py:219-224                ||q[:2] - goal|| <= epsilon, per scenario
+    per-stage FreeSpaceDecomposition in Python, :191-203         fsd_points=... -> rmpc_fsd_constraints on the previous plan
+"""
+from __future__ import annotations
+
+import torch
+
+
+def plant_step(x: torch.Tensor, u: torch.Tensor, dt: float, diffdrive: bool, nodes: int = 5) -> torch.Tensor:
+    """x+ of the model the solver was generated from (robotmpcs/models/mpcModel.py:65-69,118-120 and
+    diff_drive_mpc_model.py:24-41): ERK2 = explicit midpoint, `nodes` substeps."""
+    if not diffdrive:
+        n = x.shape[1] // 2
+        q, qd = x[:, :n], x[:, n:]
+        return torch.cat([q + dt * qd + 0.5 * dt * dt * u, qd + dt * u], 1)
+    h = dt / nodes
+    x = x.clone()
+    for _ in range(nodes):
+        def f(s):
+            th, v, om = s[:, 2], s[:, 6], s[:, 7]
+            z = torch.zeros_like(th)
+            return torch.stack([torch.cos(th) * v, torch.sin(th) * v, om, z, z, z, u[:, 0], u[:, 1]], 1)
+        k1 = f(x)
+        x = x + h * f(x + 0.5 * h * k1)
+    return x
+
+
+def closed_loop(planner, x0: torch.Tensor, goal: torch.Tensor, steps: int, epsilon: float = 0.2, fsd_points=None,
+                fsd_radius: float = 5.0, on_step=None) -> dict:
+    """Runs `steps` control steps for the planner's whole batch.  x0[B,nx], goal[B,>=2] CUDA float64; the planner must
+    be device resident with its scenario parameters already set.  fsd_points[B,P,3] switches on the per-step
+    free-space decomposition (LinearConstraints models): planes for stage k are seeded from the previous plan's stage
+    k+1 pose, or from the measured pose at the first step, as boxer_example.py:191-201 does."""
+    diffdrive = planner._robotType.startswith("boxer")
+    dt = planner.dt()
+    nx, B = planner._nx, x0.shape[0]
+    n = planner._config.n
+    x = x0.clone()
+    reached = torch.zeros(B, dtype=torch.bool, device=x.device)
+    first_reached = torch.full((B,), -1, dtype=torch.int64, device=x.device)
+    iters = torch.zeros(steps, dtype=torch.float64, device=x.device)
+    failures = torch.zeros(B, dtype=torch.int64, device=x.device)
+    traj = [x[:, :2].clone()]
+    K = planner._config.number_obstacles
+    idx = [planner._paramMap[f"lin_constrs_{i}"][0] for i in range(K)] if fsd_points is not None else None
+    z_prev = None
+    for t in range(steps):
+        if fsd_points is not None:
+            if z_prev is None:
+                ref = x[:, :3].contiguous()
+            else:  # stage k of the new problem ~ stage k+1 of the previous plan
+                ref = planner._solver.shift_horizon(z_prev)
+            planner._solver.fsd_constraints(fsd_points, ref, K, fsd_radius, params=planner._params3, idx=idx, want_out=False)
+        if diffdrive:
+            action, z, flag = planner.computeAction(x[:, :n], x[:, n:2 * n], x[:, 2 * n:])
+        else:
+            action, z, flag = planner.computeAction(x[:, :n], x[:, n:])
+        info_iters = planner._last_iters if hasattr(planner, "_last_iters") else None
+        if info_iters is not None:
+            iters[t] = info_iters.to(torch.float64).mean()
+        ok = (flag >= 0)[:, None]
+        u = torch.where(ok, action, torch.zeros_like(action))   # boxer_example.py:194: a failed solve is not applied
+        failures += (flag < 0).to(torch.int64)
+        x = plant_step(x, u, dt, diffdrive)
+        z_prev = z
+        d = torch.linalg.norm(x[:, :2] - goal[:, :2], dim=1)
+        newly = (d <= epsilon) & ~reached
+        first_reached = torch.where(newly, torch.full_like(first_reached, t + 1), first_reached)
+        reached |= newly
+        traj.append(x[:, :2].clone())
+        if on_step is not None:
+            on_step(t, x, z, flag)
+    return {"x": x, "reached": reached, "first_reached": first_reached, "mean_iters": iters, "failures": failures,
+            "goal_distance": torch.linalg.norm(x[:, :2] - goal[:, :2], dim=1), "path": torch.stack(traj, 1)}

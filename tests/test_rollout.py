@@ -1,0 +1,56 @@
+"""Headless closed-loop rollout on the GPU: the batched planner in `previous_plan` mode drives the
+MPC's own model as the plant.  Size-independent properties: nobody collides, everybody approaches the goal, warm-started
+solves need fewer iterations than the cold first one, and the torch plant agrees with the solver's own prediction."""
+import os
+
+import numpy as np
+import pytest
+import yaml
+
+from conftest import CONFIG, SOLVERS
+from robot_mpcs_b200 import scenarios as sc
+
+pytestmark = pytest.mark.gpu
+
+
+def test_point_robot_closed_loop(built):
+    import torch
+    from robot_mpcs_b200.planner.mpcPlanner import MPCPlanner
+    from robot_mpcs_b200.rollout import closed_loop
+    from robot_mpcs_b200.utils.utils import parse_setup
+    B, T = 96, 60
+    setup = parse_setup(os.path.join(CONFIG, "pointRobotMpc.yaml"))["mpc"]
+    setup["initialization"] = "previous_plan"
+    pl = MPCPlanner("pointRobot", SOLVERS + os.sep, batch_size=B, device_resident=True, **setup)
+    pl.concretize()
+    pl.reset()
+    pm = yaml.safe_load(open(os.path.join(SOLVERS, "pointRobot_n3_005_H20_noSlack", "paramMap.yaml")))
+    s = sc.point_robot_sweep(pm, B, seed=5)
+    dev = torch.device("cuda:0")
+    pl._params3[:] = torch.as_tensor(s["params"], device=dev)            # scenario parameters as the set* calls leave them
+    x0 = torch.as_tensor(s["xinit"], device=dev)
+    P0 = s["params"][:, 0]
+    goal = torch.as_tensor(P0[:, pm["goal"]], device=dev)
+    obst = torch.as_tensor(P0[:, pm["obst"]], device=dev)
+    rb = float(P0[0, pm["r_body"][0]])
+    clear, pred_err = [], []
+
+    def on_step(t, x, z, flag):
+        # pointRobot FK: base_link sits 0.05 above the plane the obstacle centre lies in
+        d = torch.sqrt(((x[:, :2] - obst[:, :2]) ** 2).sum(1) + 0.05 ** 2) - obst[:, 3] - rb
+        clear.append(d.min())
+        ok = flag == 1
+        pred_err.append((z[ok, 1, :6] - x[ok]).abs().max())               # plant == the solver's own stage-2 state
+
+    r = closed_loop(pl, x0, goal, T, epsilon=0.2, on_step=on_step)
+    d0 = torch.linalg.norm(x0[:, :2] - goal[:, :2], dim=1)
+    assert float(torch.stack(clear).min()) > -1e-6                        # no collision along any path
+    assert float(torch.stack(pred_err).max()) < 1e-9
+    assert int(r["failures"].sum()) == 0
+    prog = (r["goal_distance"] < d0 - 0.5) | (r["goal_distance"] < 0.6) | r["reached"]
+    assert float(prog.double().mean()) > 0.8                              # starts next to the goal overshoot it (1 s horizon) ...
+    assert bool((r["goal_distance"] < d0 + 1.0).all())                    # ... but nobody runs away
+    assert float((d0 - r["goal_distance"]).mean()) > 2.0                  # 3 s at <= 1 m/s^2: metres of progress
+    it = r["mean_iters"].cpu().numpy()
+    assert it[5:].mean() < 0.9 * it[0]                                    # previous-plan warm starts pay off (12.3 -> 10.2)
+    assert r["path"].shape == (B, T + 1, 2)
