@@ -153,7 +153,9 @@ struct StageShared {
   // [Qd | Hd | .. | g1 | gl | g0]: dense Hessian part (Dims::qidx), diagonal entries of the variables NDS..NVAR-1,
   // g1 = -G'(1/s) (coefficient of mu in the barrier gradient), gl = cost gradient - G' lambda, g0 = cost gradient.
   // Everything before g0 is dead once phase 1 of the sweep has consumed it; K | kff0 | kff1 then reuse that space.
-  T Qs[Dims<M>::OFF0 + M::NVAR];
+  // After the roll-out the same array is scratch for the line search: row values of the trial point in [0, NH), multiplier
+  // steps in [NH, 2 NH).
+  T Qs[Dims<M>::OFF0 + M::NVAR > 2 * M::NH ? Dims<M>::OFF0 + M::NVAR : 2 * M::NH];
   T ABv[DynS<M>::NABV];      // z-dependent entries of [A B]
   T d[M::NX];                // Phi(z_k) - x_{k+1}
   T nu01[2];                 // adjoint of (X+, Y+) from the previous sweep (diff-drive curvature)
@@ -226,6 +228,7 @@ struct Ipm {
           y1[r] = trcp(sr);
           sig[r] = lr * y1[r];
           lacc.mul(sr);
+          if ((r % 12 == 11 && r + 1 < NH) || (SLOTS > 1 && r == NH - 1)) lacc.flush();
           const float cr = float(sr * lr);
           cmax = fmaxf(cmax, cr);
           cmin = fminf(cmin, cr);
@@ -595,6 +598,7 @@ struct Ipm {
       // ---- Newton step, linear step-length estimates, merit slope
       rollout(mu);
       const T tau = tmax(T(opt.tau_min), T(1) - mu);
+      const T mu_est = mu;
       float rp = 0.0f, rd = 0.0f;  // step-length caps: single precision is enough (the true rows are checked in the line search)
       T dphi = T(0);
       RMPC_UNROLL
@@ -612,6 +616,7 @@ struct Ipm {
             const T rs = trcp(sr);
             const T dlr = mu * rs - lr - (lr * rs) * dsr;
             rp = fmaxf(rp, float(-dsr * rs));             // largest relative decrease of a slack ...
+            S.st[k].Qs[NH + r] = dlr;                     // kept for the multiplier update (K, kff and g0 are dead from here on)
             rd = fmaxf(rd, fdiv_approx(-float(dlr), float(lr)));      // ... and of a multiplier, for the fraction-to-boundary rule
             dphi -= mu * dsr * rs;
           }
@@ -657,7 +662,8 @@ struct Ipm {
                 if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, k, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(s[sl][r]), double(lam[sl][r]), double(stv), double(s[sl][r] + alpha * gd[r]), double(alpha)); }
 #endif
               }
-              la.mul(tmax(stv, T(1e-300)));
+              la.mul(tmax(stv, T(0)));
+              if ((r % 12 == 11 && r + 1 < NH) || (SLOTS > 1 && r == NH - 1)) la.flush();
             }
             if (k < N - 1) {
               T xn[NX];
@@ -698,8 +704,10 @@ struct Ipm {
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
         if (k < N) {
-          T gd[NH];
-          row_dirs(sl, k, gd);
+          if (mu != mu_est) {  // the creep guard raised mu after the multiplier steps were formed: d(lambda) is linear in mu
+            RMPC_UNROLL
+            for (int r = 0; r < NH; ++r) S.st[k].Qs[NH + r] += (mu - mu_est) * trcp(s[sl][r]);
+          }
           T snv[NH];  // new slacks: the row values of the accepted trial ...
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) snv[r] = S.st[k].Qs[r];
@@ -720,9 +728,8 @@ struct Ipm {
           }
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
-            const T sr = s[sl][r], lr = lam[sl][r];
-            const T rs = trcp(sr);
-            const T dlr = mu * rs - lr - (lr * rs) * gd[r];
+            const T lr = lam[sl][r];
+            const T dlr = S.st[k].Qs[NH + r];
             const T sn = snv[r];
             T ln = lr + adu * dlr;
             const T mus = mu * trcp(sn);

@@ -124,28 +124,20 @@ void tsincos(double x, double* sn, double* cs) {
 // sum_i log(x_i) as log(prod mantissas) + ln2 * sum exponents: one log per stage instead of one per row.
 template <class T> struct LogAcc;
 template <> struct LogAcc<double> {
-  double m;
-  int e;
-  RMPC_HD LogAcc() : m(1.0), e(0) {}
-  // x > 0, normal.  Every factor is a mantissa in [0.5, 1): up to ~1000 of them stay clear of underflow (callers
-  // multiply NH * SLOTS < 100 values).
-  RMPC_HD void mul(double x) {
-#if defined(__CUDA_ARCH__)
-    const int hi = __double2hiint(x);
-    e += ((hi >> 20) & 0x7ff) - 1022;
-    m *= __hiloint2double((hi & 0x800fffff) | 0x3fe00000, __double2loint(x));
-#else
-    int ex;
-    m *= frexp(x, &ex);
-    e += ex;
-#endif
-  }
-  RMPC_HD double value() const { return tlog(m) + 0.6931471805599453 * double(e); }
+  double m, lg;
+  RMPC_HD LogAcc() : m(1.0), lg(0.0) {}
+  // x > 0.  A plain running product: the caller flushes it into a logarithm every 12 factors (flush_every), which keeps
+  // 12 slacks between 1e-16 and 1e16 clear of under- and overflow; a factor of 0 (a trial point outside the domain)
+  // gives -inf, which the line search rejects.
+  RMPC_HD void mul(double x) { m *= x; }
+  RMPC_HD void flush() { lg += tlog(m); m = 1.0; }
+  RMPC_HD double value() const { return lg + tlog(m); }
 };
 template <> struct LogAcc<float> {
   float a;
   RMPC_HD LogAcc() : a(0.0f) {}
   RMPC_HD void mul(float x) { a += logf(x); }
+  RMPC_HD void flush() {}
   RMPC_HD float value() const { return a; }
 };
 
