@@ -207,8 +207,9 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
+        # NCCL prints its version banner (NCCL_DEBUG >= VERSION) to stdout: send its log to stderr, rank 0's stdout carries
+        # exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     sdir, _, defB, f_iter, desc = WORKLOADS[args.workload]
     B = args.batch or defB
