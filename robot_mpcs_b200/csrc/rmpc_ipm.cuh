@@ -197,14 +197,14 @@ struct Ipm {
 
   // per-lane state of the stages this lane owns
   T lam[SLOTS][NH], s[SLOTS][NH];
-  bool any_shift[SLOTS];
-  float sh[SLOTS][NH];  // shifts of the rows that started infeasible (any positive number works: single precision is enough)
+  float sh[SLOTS][NH];  // shifts of the rows that started infeasible; referenced only by the <SH = true> instantiations below
   T Gg[SLOTS][NGEO1][NQ];
 
   RMPC_HD Ipm(const Group<G>& g_, ProblemShared<M, T>& S_, const ParamView<T>& pv_, const Options& o_) : g(g_), S(S_), pv(pv_), opt(o_) {}
 
 
   // ---- A: stage-parallel derivatives ----------------------------------------------------------
+  template <bool SH>
   RMPC_HD void derivs(const bool exact, const T reg, Red<T>& o) {
     LogAcc<T> lacc;
     T f = T(0), theta = T(0), res_eq = T(0), msum = T(0), smin = T(1e300);
@@ -233,12 +233,12 @@ struct Ipm {
           cmax = fmaxf(cmax, cr);
           cmin = fminf(cmin, cr);
           msum += lr;
-          shmax = fmaxf(shmax, sh[sl][r]);
+          if constexpr (SH) shmax = fmaxf(shmax, sh[sl][r]);
         }
-        if (shmax > 0.0f) {  // rows that started infeasible (rare): a slack this small next to its shift cannot recover
+        if constexpr (SH) {  // a slack this small next to its shift cannot recover
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r)
-            if (sh[sl][r] > 0.0f) smin = tmin(smin, s[sl][r] - T(1e-6f * sh[sl][r]));
+            if (sh[sl][r] > 0.0f) { smin = tmin(smin, s[sl][r] - T(1e-6f * sh[sl][r])); theta += T(sh[sl][r]); }
         }
         RMPC_UNROLL
         for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lam[sl][M::geo_row(r)]; }
@@ -269,6 +269,23 @@ struct Ipm {
         constexpr int NQD = Dims<M>::NQD;
         RMPC_UNROLL
         for (int i = 0; i < NV; ++i) { st.Qs[Dims<M>::OFF0 + i] = sd.g[i]; st.Qs[Dims<M>::OFF1 + i] = q1[i]; st.Qs[Dims<M>::OFFL + i] = glv[i]; }
+        if constexpr (SH) {
+          // A shifted row is treated like a violated equality h + shift(1 - alpha) >= 0: the Newton step is asked to
+          // remove the whole shift, ds = g'dz - shift, which adds (lambda/s) shift g to the mu-free right-hand side.
+          T q0[NV];
+          RMPC_UNROLL
+          for (int i = 0; i < NV; ++i) q0[i] = sd.g[i];
+          RMPC_UNROLL
+          for (int r = 0; r < M::NGEO; ++r) {
+            const T push = sig[M::geo_row(r)] * T(sh[sl][M::geo_row(r)]);
+            RMPC_UNROLL
+            for (int i = 0; i < NQ; ++i) q0[i] -= sd.Gg[r][i] * push;
+          }
+          RMPC_UNROLL
+          for (int r = 0; r < M::NLIM; ++r) q0[M::lim_var(r)] -= T(M::lim_sign(r)) * sig[M::lim_row(r)] * T(sh[sl][M::lim_row(r)]);
+          RMPC_UNROLL
+          for (int i = 0; i < NV; ++i) st.Qs[Dims<M>::OFF0 + i] = q0[i];
+        }
         // dense part of the Hessian (lower triangle, Dims::qidx) with the diagonal folded in
         T Qd[NQD];
         RMPC_UNROLL
@@ -307,7 +324,9 @@ struct Ipm {
       }
     }
     o.f = g.sum(f); o.theta = g.sum(theta); o.logs = g.sum(lacc.value()); o.res_eq = g.max(res_eq);
-    o.comp_min = T(g.min(cmin)); o.comp_max = T(g.max(cmax)); o.mult_sum = g.sum(msum); o.shift_max = T(g.max(shmax)); o.s_min = g.min(smin);
+    o.comp_min = T(g.min(cmin)); o.comp_max = T(g.max(cmax)); o.mult_sum = g.sum(msum); 
+    if constexpr (SH) { o.shift_max = T(g.max(shmax)); o.s_min = g.min(smin); }
+    else { o.shift_max = T(0); o.s_min = T(1); }
     o.pole = g.any(pole);
     g.sync();
   }
@@ -511,8 +530,24 @@ struct Ipm {
     for (int r = 0; r < M::NLIM; ++r) gd[M::lim_row(r)] = T(M::lim_sign(r)) * sdz[M::lim_var(r)];
   }
 
+  struct Loop {  // what one iteration hands to the next
+    T mu, rho_pen = T(1), err_ref = T(1e300);
+    T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
+    int it, ncreep = 0, it_ref = 0, gn_hold = 0, gn_len = 1;
+    Red<T> so;
+  };
+
   // ---- the solve ----------------------------------------------------------------------------------
-  RMPC_HD void solve(const T* xinit, const T* z_in, T* z_out, Info& info) {
+  // The iteration exists twice: iterate<true> knows about rows that start infeasible (shifted rows), iterate<false>
+  // does not and is smaller and cheaper in registers.  MODE picks what a build of solve() contains:
+  //   kAll      every problem (the CPU twin)
+  //   kFeasible only problems whose initial guess satisfies every row with margin delta: no shift code at all; returns
+  //             false, outputs untouched, for the others
+  //   kShifted  only the others; returns false for a problem kFeasible takes
+  // The CUDA host code runs the last two as two kernels side by side, so that the common case runs the smaller code.
+  static constexpr int kAll = 0, kFeasible = 1, kShifted = 2;
+  template <int MODE = 0>
+  RMPC_HD bool solve(const T* xinit, const T* z_in, T* z_out, Info& info) {
     // initial point: z from the guess, x_1 = xinit
     for (int e = g.lane; e < N * NV; e += G) S.st[e / NV].z[e % NV] = z_in[e];
     g.sync();
@@ -520,11 +555,10 @@ struct Ipm {
     for (int e = g.lane; e < N; e += G) { S.st[e].nu01[0] = T(0); S.st[e].nu01[1] = T(0); }
     g.sync();
     T mu = T(opt.mu0);
-    bool pole0 = false;
+    bool pole0 = false, shifted = false;
     RMPC_UNROLL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
-      any_shift[sl] = false;
       if (k < N) {
         T p[M::NPAR];
         load_params<M, T>(pv, k, p);
@@ -534,24 +568,51 @@ struct Ipm {
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
           const T hv = sv.h[r];
-          const float shift = hv >= T(opt.delta) ? 0.0f : float(T(opt.delta) - hv);
-          sh[sl][r] = shift;
-          any_shift[sl] = any_shift[sl] || shift > 0.0f;
+          // a violated row starts with a slack as large as its violation: the fraction-to-boundary rule then leaves room
+          // for steps that remove only part of the shift
+          const float shift = hv >= T(opt.delta) ? 0.0f : float(tmax(T(opt.delta), -hv) - hv);
+          if constexpr (MODE != kFeasible) sh[sl][r] = shift;
+          shifted = shifted || shift > 0.0f;
           s[sl][r] = hv + T(shift);
           lam[sl][r] = mu * trcp(hv + T(shift));
         }
       }
     }
     info.exitflag = 0;
-    int it = 0;
-    Red<T> so;
-    so.f = so.res_stat = so.res_eq = so.comp_max = so.shift_max = T(0);
-    T rho_pen = T(1);
-    int ncreep = 0, it_ref = 0, gn_hold = 0, gn_len = 1;
-    T err_ref = T(1e300);
-    T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
-    if (g.any(pole0)) { info.exitflag = -8; it = opt.max_iter + 1; }
+    Loop L;
+    L.mu = mu; L.it = 0;
+    L.so.f = L.so.res_stat = L.so.res_eq = L.so.comp_max = L.so.shift_max = T(0);
+    if (g.any(pole0)) { info.exitflag = -8; L.it = opt.max_iter + 1; }
+    // Rows that start infeasible are rare (a warm start whose obstacles moved onto the plan), and their bookkeeping
+    // costs registers and instructions in every unrolled row loop: the iteration exists twice, and the copy that
+    // knows about shifts runs only until the last shift of the problem has reached zero.
+    bool done = false;
+    if (g.any(shifted)) {
+      if constexpr (MODE != kFeasible) done = iterate<true>(L, info);
+      else return false;
+    } else if (MODE == kShifted) return false;
+    if (!done) iterate<false>(L, info);
+    finish(L, z_out, info);
+    return true;
+  }
+
+
+  // Runs iterations until the solve ends (returns true) or, for SH, until no row of the problem is shifted any more.
+  template <bool SH>
+  RMPC_HD bool iterate(Loop& L, Info& info) {
+    T mu = L.mu, rho_pen = L.rho_pen, err_ref = L.err_ref, lm = L.lm;
+    int it = L.it, ncreep = L.ncreep, it_ref = L.it_ref, gn_hold = L.gn_hold, gn_len = L.gn_len;
+    Red<T> so = L.so;
+    bool handover = false;
     for (; it <= opt.max_iter; ++it) {
+      if constexpr (SH) {
+        bool left = false;
+        RMPC_UNROLL
+        for (int sl = 0; sl < SLOTS; ++sl)
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r) left = left || sh[sl][r] > 0.0f;
+        if (!g.any(left)) { handover = true; break; }
+      }
       g.align();
       // An indefinite exact Hessian costs a whole derivative pass + sweep before the Gauss-Newton retry, and far from
       // the solution it is indefinite iteration after iteration: after a failure the exact attempt is skipped for
@@ -560,7 +621,7 @@ struct Ipm {
       if (gn_hold > 0) --gn_hold;
       T reg = T(opt.reg) + lm;
       for (int tries = 0; tries < 5; ++tries) {
-        derivs(exact, reg, so);
+        derivs<SH>(exact, reg, so);
         sweep(so);
         if (so.ok) { if (exact) gn_len = 1; break; }
         if (exact) { exact = false; gn_hold = gn_len; gn_len = gn_len < int(opt.gn_hold_max) ? 2 * gn_len : gn_len; }  // not positive definite: Gauss-Newton
@@ -612,8 +673,10 @@ struct Ipm {
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];
-            const T dsr = gd[r];
+            const T shr = SH ? T(sh[sl][r]) : T(0);
+            const T dsr = gd[r] - shr;                   // the step is asked to remove the whole shift
             const T rs = trcp(sr);
+            if constexpr (SH) dphi += (lr * rs) * shr * gd[r];   // g0 holds the cost gradient minus the shift push: undo it here
             const T dlr = mu * rs - lr - (lr * rs) * dsr;
             rp = fmaxf(rp, float(-dsr * rs));             // largest relative decrease of a slack ...
             S.st[k].Qs[NH + r] = dlr;                     // kept for the multiplier update (K, kff and g0 are dead from here on)
@@ -654,7 +717,11 @@ struct Ipm {
             bad = bad || sv.pole;
             RMPC_UNROLL
             for (int r = 0; r < NH; ++r) {
-              const T stv = sv.h[r] + T(sh[sl][r]);
+              T stv = sv.h[r];
+              if constexpr (SH) {  // same rounding as the update of sh below
+                const float shn = float((T(1) - alpha) * T(sh[sl][r]));
+                if (shn >= 1e-12f) { stv += T(shn); theta += T(shn); }
+              }
               S.st[k].Qs[r] = sv.h[r];  // kept for the update of s once the trial is accepted (K and kff are dead by now)
               if (!(stv >= (T(1) - tau) * s[sl][r])) {
                 bad = true;
@@ -711,20 +778,14 @@ struct Ipm {
           T snv[NH];  // new slacks: the row values of the accepted trial ...
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) snv[r] = S.st[k].Qs[r];
-          if (any_shift[sl]) {  // ... plus, for rows that started infeasible (rare), a shift that shrinks while keeping s >= s/2
-            bool left = false;
+          if constexpr (SH) {  // ... plus, for rows that started infeasible, what is left of their shift after a step of length alpha
             RMPC_UNROLL
             for (int r = 0; r < NH; ++r) {
-              const T sho = T(sh[sl][r]);
-              if (sho > T(0)) {
-                const T sn = snv[r] + sho;
-                const float shn = float(tmax(T(0), sho - T(0.5) * sn));
-                snv[r] = sn - (sho - T(shn));
-                sh[sl][r] = shn;
-                left = left || shn > 0.0f;
-              }
+              float shn = float((T(1) - alpha) * T(sh[sl][r]));
+              if (shn < 1e-12f) shn = 0.0f;
+              snv[r] += T(shn);
+              sh[sl][r] = shn;
             }
-            any_shift[sl] = left;
           }
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
@@ -743,15 +804,22 @@ struct Ipm {
       }
       g.sync();
     }
+    L.mu = mu; L.rho_pen = rho_pen; L.err_ref = err_ref; L.lm = lm;
+    L.it = it; L.ncreep = ncreep; L.it_ref = it_ref; L.gn_hold = gn_hold; L.gn_len = gn_len;
+    L.so = so;
+    return !handover;
+  }
+
+  RMPC_HD void finish(const Loop& L, T* z_out, Info& info) {
     if (z_out)
       for (int e = g.lane; e < N * NV; e += G) z_out[e] = S.st[e / NV].z[e % NV];
-    info.iters = it > opt.max_iter ? opt.max_iter : it;
-    info.obj = double(so.f);
-    info.res_stat = double(so.res_stat);
-    info.res_eq = double(so.res_eq);
-    info.res_ineq = double(so.shift_max);
-    info.res_comp = double(so.comp_max);
-    info.mu = double(mu);
+    info.iters = L.it > opt.max_iter ? opt.max_iter : L.it;
+    info.obj = double(L.so.f);
+    info.res_stat = double(L.so.res_stat);
+    info.res_eq = double(L.so.res_eq);
+    info.res_ineq = double(L.so.shift_max);
+    info.res_comp = double(L.so.comp_max);
+    info.mu = double(L.mu);
   }
 };
 

@@ -36,13 +36,20 @@ static std::atomic<long> g_launches{0};
     }                                                                                              \
   } while (0)
 
+constexpr int kSideStreams = 4;
+
 struct rmpc_solver {
   int device;
   int max_batch;
   rmpc_options opt;
   int* counter;       // device work-queue heads, one per in-flight call slot (round robin)
   int counter_slot;
-  int blocks_per_sm, sm_count;
+  int blocks_per_sm, blocks_per_sm_sh, sm_count;
+  // the kernel for infeasible starts runs on a side stream, forked from and joined to the caller's stream; a few of
+  // them in rotation, so that calls on different streams do not queue behind each other here
+  cudaStream_t side[kSideStreams];
+  cudaEvent_t ev_fork[kSideStreams], ev_join[kSideStreams];
+  int side_slot;
   double* z_tmp;      // scratch plan for the in-place horizon shift
   int* d_idx;         // scratch for rmpc_set_params
   int d_idx_cap;
@@ -78,10 +85,39 @@ static_assert(kWarps >= 1, "one problem does not fit into the shared memory of a
 #ifndef RMPC_MIN_BLOCKS
 #define RMPC_MIN_BLOCKS 1   // resident blocks per SM the register allocation must allow
 #endif
+struct SolveArgs {
+  const double *xinit, *x0, *params;
+  double *z_out, *action;
+  rmpc_info info;
+  Options opt;
+  int control_mode;
+};
+
+__device__ __forceinline__ void write_outputs(const SolveArgs& a, const Shared& S, int lane, int b, const Info& inf) {
+  if (a.action && lane < M::NU) {
+    // "acc": u of stage 1; "vel": z_2[nvar-2nu : nvar-nu]  (planner/mpcPlanner.py:275-281)
+    a.action[(size_t)b * M::NU + lane] =
+        a.control_mode == 0 ? S.st[0].z[M::NX + lane] : S.st[1].z[M::NVAR - 2 * M::NU + lane];
+  }
+  if (lane == 0) {
+    if (a.info.exitflag) a.info.exitflag[b] = inf.exitflag;
+    if (a.info.iters) a.info.iters[b] = inf.iters;
+    if (a.info.obj) a.info.obj[b] = inf.obj;
+    if (a.info.res_stat) a.info.res_stat[b] = inf.res_stat;
+    if (a.info.res_eq) a.info.res_eq[b] = inf.res_eq;
+    if (a.info.res_ineq) a.info.res_ineq[b] = inf.res_ineq;
+    if (a.info.res_comp) a.info.res_comp[b] = inf.res_comp;
+  }
+}
+
+// Two instantiations, launched side by side on two streams.  kFeasible is the common case and contains no code for
+// rows that start infeasible; kShifted carries both copies of the iteration and solves only problems whose initial guess
+// violates a row (for a feasible batch it evaluates each problem's rows once and exits).  Each problem is solved and
+// written by exactly one of the two.  With the rare path in the same kernel as the hot one the solver was 4-10 %
+// slower (inlined) or 25 % slower (as a called function); B200, r1l A/B in DESIGN.md.
+template <int MODE>
 __global__ void __launch_bounds__(32 * kWarps, RMPC_MIN_BLOCKS)
-solve_kernel(int B, const double* __restrict__ xinit, const double* __restrict__ x0, const double* __restrict__ params,
-             double* __restrict__ z_out, double* __restrict__ action, rmpc_info info, Options opt, int control_mode,
-             int* __restrict__ counter) {
+solve_kernel(int B, const __grid_constant__ SolveArgs a, int* __restrict__ counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5;
   Shared& S = *reinterpret_cast<Shared*>(smem_raw + warp * kSharedPerWarp);
@@ -95,27 +131,15 @@ solve_kernel(int B, const double* __restrict__ xinit, const double* __restrict__
       if (kWarps > 1) while (!__syncthreads_and(1)) {}
       break;
     }
-    const ParamView<double> pv{params + (size_t)b * M::N * M::NPAR, M::NPAR, 1};
+    const ParamView<double> pv{a.params + (size_t)b * M::N * M::NPAR, M::NPAR, 1};
     Info inf;
+    bool mine;
     {
-      Ipm<M, double, 32> ipm(g, S, pv, opt);
-      ipm.solve(xinit + (size_t)b * M::NX, x0 + (size_t)b * M::N * M::NVAR,
-                z_out ? z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
+      Ipm<M, double, 32> ipm(g, S, pv, a.opt);
+      mine = ipm.template solve<MODE>(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR,
+                                      a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
     }
-    if (action && g.lane < M::NU) {
-      // "acc": u of stage 1; "vel": z_2[nvar-2nu : nvar-nu]  (planner/mpcPlanner.py:275-281)
-      action[(size_t)b * M::NU + g.lane] =
-          control_mode == 0 ? S.st[0].z[M::NX + g.lane] : S.st[1].z[M::NVAR - 2 * M::NU + g.lane];
-    }
-    if (g.lane == 0) {
-      if (info.exitflag) info.exitflag[b] = inf.exitflag;
-      if (info.iters) info.iters[b] = inf.iters;
-      if (info.obj) info.obj[b] = inf.obj;
-      if (info.res_stat) info.res_stat[b] = inf.res_stat;
-      if (info.res_eq) info.res_eq[b] = inf.res_eq;
-      if (info.res_ineq) info.res_ineq[b] = inf.res_ineq;
-      if (info.res_comp) info.res_comp[b] = inf.res_comp;
-    }
+    if (mine) write_outputs(a, S, g.lane, b, inf);
     __syncwarp();
   }
 }
@@ -182,6 +206,11 @@ static int free_all(rmpc_solver* s) {
   cudaFree(s->d_idx); cudaFree(s->h_xinit); cudaFree(s->h_x0); cudaFree(s->h_params); cudaFree(s->h_z);
   cudaFree(s->h_action); cudaFree(s->h_res); cudaFree(s->h_flag);
   if (s->hstream) cudaStreamDestroy(s->hstream);
+  for (int i = 0; i < kSideStreams; ++i) {
+    if (s->side[i]) cudaStreamDestroy(s->side[i]);
+    if (s->ev_fork[i]) cudaEventDestroy(s->ev_fork[i]);
+    if (s->ev_join[i]) cudaEventDestroy(s->ev_join[i]);
+  }
   cudaFreeHost(s->p_z); cudaFreeHost(s->p_action); cudaFreeHost(s->p_res); cudaFreeHost(s->p_flag);
   return 0;
 }
@@ -209,15 +238,24 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
   if ((e = cudaMalloc(&s->counter, sizeof(int) * kCounterSlots)) != cudaSuccess) return fail("cudaMalloc", e);
   const size_t smem = kSharedPerWarp * kWarps;
-  if ((e = cudaFuncSetAttribute(solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+  using I = Ipm<M, double, 32>;
+  if ((e = cudaFuncSetAttribute(solve_kernel<I::kFeasible>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(solve_kernel<I::kShifted>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
     return fail("cudaFuncSetAttribute(shared memory)", e);
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel, 32 * kWarps, smem)) != cudaSuccess)
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel<I::kFeasible>, 32 * kWarps, smem)) != cudaSuccess ||
+      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_sh, solve_kernel<I::kShifted>, 32 * kWarps, smem)) != cudaSuccess)
     return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor", e);
+  for (int i = 0; i < kSideStreams; ++i) {
+    if ((e = cudaStreamCreateWithFlags(&s->side[i], cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&s->ev_fork[i], cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming)) != cudaSuccess)
+      return fail("cudaEventCreate", e);
+  }
   if (const char* cap = getenv("RMPC_MAX_BLOCKS_PER_SM")) {  // experiment knob: fewer problems in flight per SM
     const int c = atoi(cap);
     if (c > 0 && c < s->blocks_per_sm) s->blocks_per_sm = c;
   }
-  if (s->blocks_per_sm < 1) { snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem); free_all(s); delete s; return nullptr; }
+  if (s->blocks_per_sm < 1 || s->blocks_per_sm_sh < 1) { snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem); free_all(s); delete s; return nullptr; }
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
   s->sm_count = prop.multiProcessorCount;
@@ -256,19 +294,33 @@ int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x
   if (s->opt.precision != 0) { snprintf(g_err, sizeof g_err, "precision %d is not available in this build (float64 only)", s->opt.precision); return -1; }
   CK(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
-  int* counter = s->counter + s->counter_slot;
-  s->counter_slot = (s->counter_slot + 1) % kCounterSlots;
-  CK(cudaMemsetAsync(counter, 0, sizeof(int), st));
-  rmpc_info inf;
-  memset(&inf, 0, sizeof inf);
-  if (info) inf = *info;
-  const Options c = to_core(s->opt);
-  // persistent grid: as many blocks as fit at once, never more than the problems need
-  long grid = (long)s->blocks_per_sm * s->sm_count;
+  int* counter = s->counter + s->counter_slot;   // two queue heads per call
+  s->counter_slot = (s->counter_slot + 2) % kCounterSlots;
+  CK(cudaMemsetAsync(counter, 0, 2 * sizeof(int), st));
+  SolveArgs a;
+  a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
+  memset(&a.info, 0, sizeof a.info);
+  if (info) a.info = *info;
+  a.opt = to_core(s->opt);
+  a.control_mode = s->opt.control_mode;
+  using I = Ipm<M, double, 32>;
   const long need = ((long)B + kWarps - 1) / kWarps;
+  // fork: infeasible starts on the side stream, next to ...
+  const int ss = s->side_slot;
+  s->side_slot = (ss + 1) % kSideStreams;
+  CK(cudaEventRecord(s->ev_fork[ss], st));
+  CK(cudaStreamWaitEvent(s->side[ss], s->ev_fork[ss], 0));
+  long grid = (long)s->blocks_per_sm_sh * s->sm_count;
   if (grid > need) grid = need;
-  solve_kernel<<<(unsigned)grid, 32 * kWarps, kSharedPerWarp * kWarps, st>>>(B, xinit, x0, params, z_out, action_out, inf, c,
-                                                                                   s->opt.control_mode, counter);
+  solve_kernel<I::kShifted><<<(unsigned)grid, 32 * kWarps, kSharedPerWarp * kWarps, s->side[ss]>>>(B, a, counter + 1);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(s->ev_join[ss], s->side[ss]));
+  // ... the common case on the caller's stream.  Persistent grid: as many blocks as fit at once, never more than the problems need
+  grid = (long)s->blocks_per_sm * s->sm_count;
+  if (grid > need) grid = need;
+  solve_kernel<I::kFeasible><<<(unsigned)grid, 32 * kWarps, kSharedPerWarp * kWarps, st>>>(B, a, counter);
+  CK(cudaStreamWaitEvent(st, s->ev_join[ss], 0));
   g_launches++;
   CK(cudaGetLastError());
   return 0;

@@ -252,3 +252,52 @@ def test_device_reciprocals(built):
     assert float(((rcp * x) - 1).abs().max()) < 1e-15
     assert float((rcp / (1.0 / x) - 1).abs().max()) < 1e-15
     assert float((rsq / torch.rsqrt(x) - 1).abs().max()) < 1e-15
+
+
+@pytest.mark.gpu
+def test_infeasible_warm_start_recovers(built):
+    """The previous plan as initial guess after an obstacle has moved onto it (diff-drive model, wconstr = 0 so the
+    cost has no pole at h = 0): rows with h < 0 start with slack = violation and a shift the Newton step is asked to
+    remove; shifts reach zero, the result is feasible and matches the twin.  Convergence bars by depth of violation
+    measured on the twin: 99 % (up to 0.12 m), 97 % (up to 0.3 m); deeper starts may end in -7 and are reported so."""
+    import torch
+    from oracle.build_twin import Twin
+    from oracle.nlp import load_model
+    sdir, B = "boxer_n3_01_H30_noSlack", 512
+    pm = _pm(sdir)
+    s = sc.boxer_radial(pm, B, seed=9)
+    solver = _solver(sdir, B)
+    d = _to_dev(s)
+    first = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    assert bool((first["exitflag"] == 1).all())
+    z1 = first["z"].cpu().numpy()
+    # obstacle 0 (radius 0.3, body 0.6) is put 0.8 m beside stage 18 of the plan: that stage violates by 0.1 m, its neighbours by more
+    ee = z1[:, :, 0:2] + 0.4 * np.stack([np.cos(z1[:, :, 2]), np.sin(z1[:, :, 2])], 2)
+    t = ee[:, 19] - ee[:, 17]
+    t /= np.linalg.norm(t, axis=1, keepdims=True) + 1e-12
+    c = ee[:, 18] + 0.8 * np.stack([-t[:, 1], t[:, 0]], 1)
+    P = s["params"].copy()
+    oi = pm["obst"][0]
+    P[:, :, oi:oi + 2] = c[:, None, :]
+    P[:, :, oi + 2] = 0.0
+    P[:, :, oi + 3] = 0.3
+    model = load_model(os.path.join(CONFIG, "boxerRadialMpc.yaml"))
+    hh = model.ineq(torch.as_tensor(z1), torch.as_tensor(P)).numpy()
+    h0 = hh.reshape(B, -1).min(1)
+    start_ok = hh[:, 0, :5].min(1) > 0.05                                # the measured state itself must be collision free
+    assert (h0 < -0.09).all()
+    r = solver.solve_batch(d["xinit"], torch.as_tensor(z1, device="cuda:0"), torch.as_tensor(P, device="cuda:0"))
+    ef = r["exitflag"].cpu().numpy()
+    z = r["z"].cpu().numpy()
+    mild = start_ok & (h0 > -0.3)
+    assert mild.sum() > 300 and (ef[mild] == 1).mean() >= 0.96, (mild.sum(), (ef[mild] == 1).mean())
+    assert set(np.unique(ef[start_ok])) <= {1, 0, -5, -7}
+    ok = start_ok & (ef == 1)
+    assert float(model.ineq(torch.as_tensor(z[ok]), torch.as_tensor(P[ok])).min()) > -1e-9
+    assert float(r["res_ineq"].cpu().numpy()[ok].max()) <= 1e-8            # no shift left
+    tw = Twin(os.path.join(SOLVERS, sdir)).solve(s["xinit"], z1, P)
+    assert (tw["exitflag"][start_ok] == ef[start_ok]).mean() > 0.95
+    both = ok & (tw["exitflag"] == 1) & (np.abs(tw["iters"] - r["iters"].cpu().numpy()) <= 2)
+    assert both.sum() > 300
+    err = np.abs(z[both] - tw["z"][both]).max(axis=(1, 2)) / np.abs(tw["z"][both]).max(axis=(1, 2))
+    assert np.median(err) < 1e-6
