@@ -41,8 +41,11 @@ WORKLOADS = {
 }
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one solve_kernel launch at the default batch (ncu --set full), and where it is kept
-NCU_TRAFFIC = {"boxer_radial": (53.718784e6 + 0.664064e6, "profiles/r1g_boxer_radial_B4096.txt")}
+# dram__bytes_read.sum + dram__bytes_write.sum of one solve at the default batch (ncu --set full, each kernel captured
+# alone with a cold L2), and where it is kept.  A solve is two concurrent launches: solve_kernel<1> (feasible starts,
+# 13.3 ms alone) and solve_kernel<2> (infeasible starts: for this workload it reads every problem once, finds none and
+# exits after 38 us).  Both read the inputs, hence twice the algorithmic bytes when neither finds them in L2.
+NCU_TRAFFIC = {"boxer_radial": ((52.709376e6 + 0.701184e6) + (52.524288e6 + 0.375552e6), "profiles/r1l_ncu_boxer_radial_B4096.txt")}
 
 
 def load_paramMap(sdir):

@@ -119,7 +119,13 @@ struct ParamView {
   const T* base;
   long stage_stride;  // elements between consecutive stages
   long elem_stride;   // elements between consecutive parameters
-  RMPC_HD T get(int k, int j) const { return base[k * stage_stride + j * elem_stride]; }
+  RMPC_HD T get(int k, int j) const {
+#if defined(__CUDA_ARCH__) && defined(RMPC_PARAM_LOAD)
+    return RMPC_PARAM_LOAD(base + k * stage_stride + j * elem_stride);   // experiment: __ldcg / __ldcs / __ldg
+#else
+    return base[k * stage_stride + j * elem_stride];
+#endif
+  }
 };
 
 template <class M, class T>
