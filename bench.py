@@ -48,6 +48,14 @@ WORKLOADS = {
 NCU_TRAFFIC = {"boxer_radial": ((52.709376e6 + 0.701184e6) + (52.524288e6 + 0.375552e6), "profiles/r1l_ncu_boxer_radial_B4096.txt")}
 
 
+_OUT = None
+
+
+def emit(line):
+    """The one JSON line of the contract, on the process's original stdout."""
+    print(json.dumps(line), file=_OUT or sys.stdout, flush=True)
+
+
 def load_paramMap(sdir):
     import yaml
     with open(os.path.join(SOLVERS, sdir, "paramMap.yaml")) as f:
@@ -193,7 +201,7 @@ def run_reference(args):
             "cpu_baseline": base, "e2e": {"value": val, "unit": "converged solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     if args.latency_samples > 0:
         line["single_solve_latency"] = dict(cpu_single_solve_latency(args.workload, args.latency_samples), path="CPU twin, 1 thread, B=1")
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -210,9 +218,6 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # NCCL prints its version banner (NCCL_DEBUG >= VERSION) to stdout: send its log to stderr, rank 0's stdout carries
-        # exactly one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     sdir, _, defB, f_iter, desc = WORKLOADS[args.workload]
     B = args.batch or defB
@@ -393,7 +398,7 @@ def run_ours(args):
             line["single_solve_latency"] = lat
             if world == 1 and not args.no_cpu_baseline:
                 line["cpu_baseline"]["single_solve_latency"] = cpu_single_solve_latency(args.workload, args.latency_samples)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -415,6 +420,12 @@ def main():
     ap.add_argument("--latency-samples", type=int, default=300, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    # Libraries write to file descriptor 1 behind Python's back (NCCL's version banner at NCCL_DEBUG=VERSION ignores
+    # NCCL_DEBUG_FILE): from here on fd 1 is stderr, and the JSON line goes to a private copy of the real stdout.
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

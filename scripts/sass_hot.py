@@ -1,16 +1,17 @@
 """Join an ncu SASS source page (csv) with nvdisasm --print-line-info to rank source lines by executed instructions,
-stall samples and local-memory traffic.  usage: sass_hot.py <src.csv> <dis.txt> [top]"""
+stall samples and local-memory traffic.  usage: sass_hot.py <src.csv> <dis.txt> [top] [substring of the function's .text section name]"""
 import csv, re, sys, collections
 rows = list(csv.reader(open(sys.argv[1])))
 head = rows[1]
 ci = {n: i for i, n in enumerate(head)}
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+fn = sys.argv[4] if len(sys.argv) > 4 else 'solve_kernel'
 # address -> line
 line_of = {}
 cur = None
 infunc = False
 for l in open(sys.argv[2]):
-    if '.text.' in l and 'solve_kernel' in l: infunc = True
+    if '.text.' in l: infunc = fn in l
     m = re.search(r'//## File "([^"]+)", line (\d+)', l)
     if m: cur = (m.group(1).split('/')[-1], int(m.group(2)))
     m = re.match(r'\s*/\*([0-9a-f]{4,})\*/\s+(\S.*?);', l)
