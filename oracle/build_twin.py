@@ -53,3 +53,12 @@ class Twin:
                                   self._p(res), self._p(o) if o is not None else None, nthreads, precision)
         return {"z": z, "exitflag": ef, "iters": it, "obj": res[:, 0], "res_stat": res[:, 1], "res_eq": res[:, 2],
                 "res_ineq": res[:, 3], "res_comp": res[:, 4], "mu": res[:, 5]}
+
+    def eval_stage(self, z, p):
+        """(J(z, p), h(z, p)) of one stage through csrc/rmpc_model.cuh:stage_values — the model code the kernel compiles."""
+        z = np.ascontiguousarray(z, dtype=np.float64)
+        p = np.ascontiguousarray(p, dtype=np.float64)
+        f = ctypes.c_double(0.0)
+        h = np.zeros(self.nh)
+        self.lib.twin_stage_values(self._p(z), self._p(p), ctypes.byref(f), self._p(h))
+        return f.value, h

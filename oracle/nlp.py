@@ -2,9 +2,15 @@
 
 Float64 CPU restatement of the NLP that robotmpcs builds symbolically with CasADi.  Written with
 torch.float64 on the CPU so that exact first derivatives come from autograd (the role CasADi AD plays
-in the reference).  PARITY UNPINNED: the reference ships no golden vectors and its solver stack
-(FORCESPRO / casadi / forwardkinematics) is absent here; the pins are the FK anchors,
-paramMap tables and the config-1 solution recorded in SURVEY.md §3.5/§7 and checked in tests/.
+in the reference).
+
+PINNED to outputs of the reference itself, run here: tests/golden/model_reference.json holds what the reference's own
+model classes return for inequalities, stage / terminal cost, continuous dynamics, paramMap, dimensions, bounds and
+solver name (tests/golden/make_model_golden.py: CasADi replaced by the same arithmetic on numbers);
+tests/test_model_reference.py checks this file against them to rounding.
+NOT PINNED (third-party code absent here and on the GPU box): the URDF forward kinematics
+(forwardkinematics 1.1.5 — ChainFk below restates the URDF convention; FK anchors of SURVEY.md §3.5 in
+tests/test_oracle_model.py), the ERK2 tableau and the solve itself (FORCESPRO; see solve.py).
 
 Each function cites the reference file:line it restates (paths relative to /root/reference).
 """

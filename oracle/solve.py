@@ -1,7 +1,7 @@
 """ORACLE — test infrastructure only.  Solves the restated NLP (oracle/nlp.py) on the CPU in float64 with
 scipy SLSQP (exact autograd gradients), optionally cross-checked by trust-constr, and certifies any
 candidate solution with a solver-independent KKT check.  This is the stand-in named in BASELINE.md §2
-for forcespro.nlp.Solver.solve (call site planner/mpcPlanner.py:262).  PARITY UNPINNED (see nlp.py).
+for forcespro.nlp.Solver.solve (call site planner/mpcPlanner.py:262).  PARITY UNPINNED for the solve: FORCESPRO is proprietary and absent, the reference holds no solutions (the NLP it is given is pinned, see nlp.py).
 """
 from __future__ import annotations
 

@@ -1,0 +1,70 @@
+"""The NLP definition against the REFERENCE'S OWN model classes.
+
+tests/golden/model_reference.json holds what /root/reference/robotmpcs/models/* themselves return — `eval_inequalities`,
+`eval_objectives`, `eval_objectiveN`, `continuous_dynamics` on seeded numeric points, and the paramMap / dimensions /
+bounds / solver name their constructors build — with CasADi replaced by the same arithmetic on numbers and the URDF
+forward kinematics supplied by oracle/nlp.py:ChainFk (tests/golden/make_model_golden.py states exactly what that does and
+does not pin).  Checked here:
+  * oracle/nlp.py (the restatement every parity test leans on) reproduces rows, cost and dynamics to rounding;
+  * the generated solver directories carry the reference's paramMap, npar, nx, nu, nh and solver name;
+  * the CPU twin — the same model code the CUDA kernel compiles (csrc/rmpc_model.cuh) — evaluates the same rows and cost.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import yaml
+
+from conftest import CONFIG, GOLDEN, SOLVERS
+from oracle.nlp import load_model
+
+G = json.load(open(os.path.join(GOLDEN, "model_reference.json")))
+CFGS = [k for k in G if k.endswith(".yaml")]
+
+
+@pytest.mark.parametrize("cfg", CFGS)
+def test_oracle_restates_reference_functions(cfg):
+    g = G[cfg]
+    m = load_model(os.path.join(CONFIG, cfg))
+    assert m.paramMap == g["paramMap"] and m.npar == g["npar"] and m.nh == g["nh"] == g["model_nh"] == len(g["samples"][0]["h"])
+    assert (m.nx, m.nu, m.n, m.nvar) == (g["nx"], g["nu"], g["n"], g["nvar"]) and g["neq"] == m.nx
+    assert m.solver_name() == g["solverName"]
+    assert g["integrator"] == ["ERK2", m.dt, 5]                                     # mpcModel.py:118-120
+    assert g["lb"] == [-100.0] * m.nvar and g["ub"] == [100.0] * m.nvar             # mpcModel.py:23-28,97-104
+    assert np.array_equal(np.array(g["E"]), np.eye(m.nx, m.nvar))                   # mpcModel.py:87-90
+    for s in g["samples"]:
+        z, p = torch.tensor(s["z"], dtype=torch.float64), torch.tensor(s["p"], dtype=torch.float64)
+        h = m.ineq(z, p).numpy()
+        assert np.allclose(h, np.array(s["h"]), rtol=1e-12, atol=1e-12)
+        J = float(m.stage_cost(z, p))
+        assert abs(J - s["J"]) <= 1e-11 * max(1.0, abs(s["J"])) and s["JN"] == s["J"]   # terminal cost = stage cost (ObjectiveManager.py:44-46)
+        xd = m.f_cont(z[: m.nx], z[m.nx:]).numpy()
+        assert np.allclose(xd, np.array(s["xdot"]), rtol=0, atol=1e-15)
+
+
+@pytest.mark.parametrize("cfg", CFGS)
+def test_generated_solver_directory_matches_reference_model(cfg, built):
+    g = G[cfg]
+    d = os.path.join(SOLVERS, g["solverName"])
+    assert os.path.isdir(d), d                                                       # same directory name as mpcModel.py:111-113
+    assert yaml.safe_load(open(os.path.join(d, "paramMap.yaml"))) == g["paramMap"]
+    props = yaml.safe_load(open(os.path.join(d, "properties.yaml")))
+    assert (props["nx"], props["nu"], props["npar"], props["ns"], props["m"]) == (g["nx"], g["nu"], g["npar"], 0, 3)
+    mj = json.load(open(os.path.join(d, "model.json")))
+    assert (mj["nh"], mj["npar"], mj["nx"], mj["nu"]) == (g["nh"], g["npar"], g["nx"], g["nu"])
+
+
+@pytest.mark.parametrize("cfg", CFGS)
+def test_kernel_model_code_matches_reference_functions(cfg, built):
+    """csrc/rmpc_model.cuh through the twin's evaluation entry point: rows and stage cost at the reference's points."""
+    from oracle.build_twin import Twin
+    g = G[cfg]
+    tw = Twin(os.path.join(SOLVERS, g["solverName"]))
+    if not hasattr(tw, "eval_stage"):
+        pytest.skip("twin has no stage-evaluation entry point")
+    for s in g["samples"]:
+        f, h = tw.eval_stage(np.array(s["z"]), np.array(s["p"]))
+        assert np.allclose(h, np.array(s["h"]), rtol=1e-11, atol=1e-12)
+        assert abs(f - s["J"]) <= 1e-10 * max(1.0, abs(s["J"]))
