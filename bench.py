@@ -143,12 +143,14 @@ def cpu_baseline(workload, B_sample, seed, threads=0):
     sdir = WORKLOADS[workload][0]
     tw = Twin(os.path.join(SOLVERS, sdir))
     s = make_inputs(workload, B_sample, seed)
+    if threads <= 0:   # every host core this process may use, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
+        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     tw.solve(s["xinit"][:64], s["x0"][:64], s["params"][:64], nthreads=threads)  # warm-up
     t = time.perf_counter()
     r = tw.solve(s["xinit"], s["x0"], s["params"], nthreads=threads)
     dt = time.perf_counter() - t
     conv = int((r["exitflag"] == 1).sum())
-    cores = tw.lib.twin_max_threads()
+    cores = threads
     return {"value": conv / dt, "unit": "converged solves/s", "cores": cores, "kind": "port",
             "sample": f"{B_sample} scenarios of workload {workload} (seed {seed}), one pass, {dt:.2f} s, converged {conv}/{B_sample}, "
                       f"mean iters {float(r['iters'].mean()):.1f}"}, dt, conv
