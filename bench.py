@@ -241,8 +241,9 @@ def run_ours(args):
     def step_device(i):
         _, d = sets[i % nsets]
         r = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
-        a, f, it = gather_results(r["action"], r["exitflag"], r["iters"], B * world) if world > 1 else (r["action"], r["exitflag"], r["iters"])
-        return r, f, it
+        # the gather runs on NCCL's stream behind this step's solve; the step's stream is not held until every rank arrives
+        g = gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True) if world > 1 else None
+        return r, g
 
     def barrier():
         if world > 1:
@@ -257,14 +258,19 @@ def run_ours(args):
         e0.record(main)
         for st in streams:
             st.wait_event(e0)
-        res = []
+        res, gathers = [], []
         for i in range(n):
             with torch.cuda.stream(streams[i % nstreams]):
-                res.append(step_device(i)[0])
+                r, g = step_device(i)
+                res.append(r)
+                gathers.append(g)
         for st in streams:
             ev = torch.cuda.Event()
             ev.record(st)
             main.wait_event(ev)
+        for g in gathers:   # every step's all_gather has delivered before the clock stops
+            if g is not None:
+                g.wait()
         e1.record(main)
         return e0, e1, res
 

@@ -16,8 +16,23 @@ def shard_bounds(B: int, rank: int, world: int) -> Tuple[int, int]:
     return lo, min(B, lo + per)
 
 
-def gather_results(action: torch.Tensor, exitflag: torch.Tensor, iters: torch.Tensor, B: int):
-    """all_gather of the per-rank results (padded to the common shard size); returns full-batch tensors."""
+class PendingGather:
+    """An all_gather in flight on NCCL's own stream; wait() makes the current stream wait for it and unpacks."""
+
+    def __init__(self, work, out, B, nu):
+        self._work, self._out, self._B, self._nu = work, out, B, nu
+
+    def wait(self):
+        if self._work is not None:
+            self._work.wait()
+        out, nu = self._out[: self._B], self._nu
+        return out[:, :nu].contiguous(), out[:, nu].to(torch.int32), out[:, nu + 1].to(torch.int32)
+
+
+def gather_results(action: torch.Tensor, exitflag: torch.Tensor, iters: torch.Tensor, B: int, async_op: bool = False):
+    """all_gather of the per-rank results (padded to the common shard size); returns full-batch tensors, or with
+    async_op a PendingGather: the stream that ran the solve is then not held up until every rank has arrived (a
+    throughput loop waits for its gathers once, at the end; a control loop that needs the actions waits at once)."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
         return action, exitflag, iters
     world = dist.get_world_size()
@@ -30,6 +45,6 @@ def gather_results(action: torch.Tensor, exitflag: torch.Tensor, iters: torch.Te
     buf[:n, nu] = exitflag.to(torch.float64)
     buf[:n, nu + 1] = iters.to(torch.float64)
     out = torch.empty(world * per, nu + 2, dtype=torch.float64, device=action.device)
-    dist.all_gather_into_tensor(out, buf)
-    out = out[:B]
-    return out[:, :nu].contiguous(), out[:, nu].to(torch.int32), out[:, nu + 1].to(torch.int32)
+    work = dist.all_gather_into_tensor(out, buf, async_op=async_op)
+    pending = PendingGather(work if async_op else None, out, B, nu)
+    return pending if async_op else pending.wait()

@@ -30,11 +30,17 @@ def _worker(rank, world, port, B, nu, out):
     flag = torch.where(idx.to(torch.int64) % 3 == 0, -7, 1).to(torch.int32)
     iters = (idx.to(torch.int64) % 17).to(torch.int32)
     a, f, it = gather_results(action, flag, iters, B)
+    # the same in flight: two gathers issued before either is waited for (a throughput loop waits once, at the end)
+    p1 = gather_results(action, flag, iters, B, async_op=True)
+    p2 = gather_results(action + 1.0, flag, iters, B, async_op=True)
+    a2, _, _ = p2.wait()
+    a1, f1, it1 = p1.wait()
+    same = torch.equal(a1, a) and torch.equal(f1, f) and torch.equal(it1, it) and torch.equal(a2, a + 1.0)
     ref = torch.arange(B, dtype=torch.float64)
     ok = (a.shape == (B, nu) and torch.equal(a, ref[:, None] * 10 + torch.arange(nu, dtype=torch.float64)[None, :])
           and torch.equal(f, torch.where(ref.to(torch.int64) % 3 == 0, -7, 1).to(torch.int32))
           and torch.equal(it, (ref.to(torch.int64) % 17).to(torch.int32)))
-    out[rank] = int(ok)
+    out[rank] = int(ok and same)
     dist.destroy_process_group()
 
 
