@@ -233,6 +233,11 @@ def run_ours(args):
         s = make_inputs(args.workload, B, seed=1000 * rank + i)
         host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in s.items()}
         devt = {k: v.to(dev) for k, v in host.items()}
+        if args.params == "compressed":
+            p3 = devt["params"].view(B, solver.N, solver.npar)
+            if not bool((p3 == p3[:, :1]).all()):
+                raise SystemExit(f"--params compressed: workload {args.workload} has stage-varying parameters")
+            devt["params"] = p3[:, 0].contiguous()
         sets.append((host, devt))
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # 256 MB > 126 MB L2
     nstreams = max(1, args.streams)
@@ -377,7 +382,7 @@ def run_ours(args):
             "metric": "converged MPC solves/sec", "value": value, "unit": "converged solves/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64" if args.precision == 0 else "f64+f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {desc}", "batch_per_gpu": B, "global_batch": B * world,
+            "config": {"workload": f"{args.workload}: {desc}", "batch_per_gpu": B, "global_batch": B * world, "params": args.params,
                        "l2": f"{nsets} rotating input sets of {set_bytes / 1e6:.0f} MB (> 126 MB L2 in total); single-batch timing with L2 flushed (256 MB write)",
                        "streams": nstreams, "stall_window": args.stall_window, "hessian": "exact+GN fallback" if args.hessian else "gauss-newton",
                        "tolerances": {k: v for k, v in solver.options().items() if k.startswith("tol")},
@@ -423,6 +428,9 @@ def main():
     ap.add_argument("--hessian", type=int, default=1)
     ap.add_argument("--ref-sample", type=int, default=4096, help="scenarios per CPU-baseline pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--params", default="reference", choices=["reference", "compressed"],
+                    help="device-resident parameter format: the reference's all_parameters[N*npar] per problem, or one npar block per problem "
+                         "for workloads whose parameters do not vary over the horizon (rmpc_solve_batch_strided, stage stride 0)")
     ap.add_argument("--streams", type=int, default=4, help="CUDA streams the consecutive batches are spread over (1 = strictly one batch at a time)")
     ap.add_argument("--stall-window", type=int, default=0, help="rmpc_options.stall_window (0 = off, the default)")
     ap.add_argument("--latency-samples", type=int, default=300, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")

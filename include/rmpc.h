@@ -75,6 +75,16 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* out);
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
                      double* z_out, double* action_out, const rmpc_info* info, void* stream);
 
+/* Same with the parameter blocks addressed by strides (in doubles): problem b, stage k reads
+ * params[b * params_batch_stride + k * params_stage_stride + j], j < npar.  The reference layout all_parameters[N * npar]
+ * (mpcPlanner.py:94,249) is (N * npar, npar).  params_stage_stride = 0 with params[B][npar] is the compressed form for
+ * scenarios whose parameters do not vary over the horizon (SURVEY.md 8f-2, B4 "or compressed"): every set* of the
+ * reference except per-stage setLinearConstraints and updateDynamicObstacles writes the same values to all N stages
+ * (mpcPlanner.py:120-210); the lanes of a warp then read one address instead of N, and the batch shrinks N-fold. */
+int rmpc_solve_batch_strided(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                             long params_batch_stride, long params_stage_stride, double* z_out, double* action_out,
+                             const rmpc_info* info, void* stream);
+
 /* Same with HOST pointers: copies inputs to the device, solves, copies results back, synchronises. */
 int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
                           double* z_out, double* action_out, const rmpc_info* info);

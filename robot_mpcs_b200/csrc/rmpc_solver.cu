@@ -87,6 +87,7 @@ static_assert(kWarps >= 1, "one problem does not fit into the shared memory of a
 #endif
 struct SolveArgs {
   const double *xinit, *x0, *params;
+  long p_bs, p_ss;   // elements between the parameter blocks of consecutive problems / stages (reference layout: N*npar, npar)
   double *z_out, *action;
   rmpc_info info;
   Options opt;
@@ -131,7 +132,7 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, int* __restrict__ count
       if (kWarps > 1) while (!__syncthreads_and(1)) {}
       break;
     }
-    const ParamView<double> pv{a.params + (size_t)b * M::N * M::NPAR, M::NPAR, 1};
+    const ParamView<double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
     Info inf;
     bool mine;
     {
@@ -289,8 +290,16 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* o) {
 
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params, double* z_out,
                      double* action_out, const rmpc_info* info, void* stream) {
+  return rmpc_solve_batch_strided(s, B, xinit, x0, params, (long)M::N * M::NPAR, (long)M::NPAR, z_out, action_out, info, stream);
+}
+
+int rmpc_solve_batch_strided(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                             long params_batch_stride, long params_stage_stride, double* z_out, double* action_out,
+                             const rmpc_info* info, void* stream) {
   if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
+  if (params_stage_stride != 0 && params_stage_stride < M::NPAR) { snprintf(g_err, sizeof g_err, "params_stage_stride %ld: 0 (one block for all stages) or >= npar = %d", params_stage_stride, M::NPAR); return -1; }
+  if (params_batch_stride < (params_stage_stride ? params_stage_stride * (M::N - 1) + M::NPAR : M::NPAR)) { snprintf(g_err, sizeof g_err, "params_batch_stride %ld too small", params_batch_stride); return -1; }
   if (s->opt.precision != 0) { snprintf(g_err, sizeof g_err, "precision %d is not available in this build (float64 only)", s->opt.precision); return -1; }
   CK(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
@@ -299,6 +308,7 @@ int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x
   CK(cudaMemsetAsync(counter, 0, 2 * sizeof(int), st));
   SolveArgs a;
   a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
+  a.p_bs = params_batch_stride; a.p_ss = params_stage_stride;
   memset(&a.info, 0, sizeof a.info);
   if (info) a.info = *info;
   a.opt = to_core(s->opt);

@@ -40,7 +40,7 @@ class RmpcInfo(ctypes.Structure):
 
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
-           "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
+           "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_strided", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
            "rmpc_set_params", "rmpc_launch_count"]
 
 
@@ -64,6 +64,8 @@ def load_library(solver_dir: str) -> ctypes.CDLL:
     lib.rmpc_set_options.argtypes = [ctypes.c_void_p, ctypes.POINTER(RmpcOptions)]
     lib.rmpc_get_options.argtypes = [ctypes.c_void_p, ctypes.POINTER(RmpcOptions)]
     lib.rmpc_solve_batch.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo), ctypes.c_void_p]
+    lib.rmpc_solve_batch_strided.argtypes = ([ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3 + [ctypes.c_long, ctypes.c_long]
+                                             + [ctypes.c_void_p] * 2 + [ctypes.POINTER(RmpcInfo), ctypes.c_void_p])
     lib.rmpc_solve_batch_host.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo)]
     lib.rmpc_solve_batch_host_async.argtypes = lib.rmpc_solve_batch_host.argtypes
     lib.rmpc_wait.argtypes = [ctypes.c_void_p]
@@ -138,7 +140,9 @@ class Solver:
     # -- batched solve -----------------------------------------------------------------------
     def solve_batch(self, xinit, x0, params, want_z=True, want_info=True, block=True):
         """xinit[B,nx], x0[B,N,nvar], params[B,N,npar] float64.  CUDA torch tensors -> device path (asynchronous on
-        the current stream, returns CUDA tensors); numpy arrays / CPU tensors -> host path (returns numpy)."""
+        the current stream, returns CUDA tensors); numpy arrays / CPU tensors -> host path (returns numpy).
+        Device path only: params[B,npar] (two dimensions) is the compressed form for parameters that do not vary over
+        the horizon (rmpc_solve_batch_strided with stage stride 0)."""
         if torch is not None and isinstance(xinit, torch.Tensor) and xinit.is_cuda:
             return self._solve_device(xinit, x0, params, want_z, want_info)
         return self._solve_host(np.asarray(xinit), np.asarray(x0), np.asarray(params), want_z, want_info, block)
@@ -149,7 +153,12 @@ class Solver:
         f64 = torch.float64
         xinit = xinit.to(f64).contiguous().view(B, self.nx)
         x0 = x0.to(f64).contiguous().view(B, self.N * self.nvar)
-        params = params.to(f64).contiguous().view(B, self.N * self.npar)
+        if params.dim() == 2 and params.shape[1] == self.npar and self.N > 1:
+            params = params.to(f64).contiguous()
+            p_bs, p_ss = self.npar, 0
+        else:
+            params = params.to(f64).contiguous().view(B, self.N * self.npar)
+            p_bs, p_ss = self.N * self.npar, self.npar
         dev = xinit.device
         z = torch.empty(B, self.N, self.nvar, dtype=f64, device=dev) if want_z else None
         act = torch.empty(B, self.nu, dtype=f64, device=dev)
@@ -163,9 +172,9 @@ class Solver:
             for k, _ in RmpcInfo._fields_:
                 setattr(info, k, out[k].data_ptr())
         stream = torch.cuda.current_stream(dev).cuda_stream
-        rc = self.lib.rmpc_solve_batch(self._h, B, xinit.data_ptr(), x0.data_ptr(), params.data_ptr(),
-                                       z.data_ptr() if want_z else None, act.data_ptr(),
-                                       ctypes.byref(info) if want_info else None, ctypes.c_void_p(stream))
+        rc = self.lib.rmpc_solve_batch_strided(self._h, B, xinit.data_ptr(), x0.data_ptr(), params.data_ptr(), p_bs, p_ss,
+                                               z.data_ptr() if want_z else None, act.data_ptr(),
+                                               ctypes.byref(info) if want_info else None, ctypes.c_void_p(stream))
         if rc != 0:
             raise SolverError("rmpc_solve_batch failed: " + self._err())
         return out

@@ -301,3 +301,25 @@ def test_infeasible_warm_start_recovers(built):
     assert both.sum() > 300
     err = np.abs(z[both] - tw["z"][both]).max(axis=(1, 2)) / np.abs(tw["z"][both]).max(axis=(1, 2))
     assert np.median(err) < 1e-6
+
+
+def test_compressed_parameter_format(built):
+    """rmpc_solve_batch_strided: one npar block per problem (stage stride 0) against the reference layout
+    all_parameters[N * npar] holding the same values in every stage — the same arithmetic, so the same bits; a stage
+    stride that is neither 0 nor >= npar is refused."""
+    import ctypes
+    import torch
+    sdir, B = "boxer_n3_01_H30_noSlack", 256
+    s = sc.boxer_radial(_pm(sdir), B, seed=3)
+    assert (s["params"] == s["params"][:, :1]).all()                 # this workload's parameters do not vary over the horizon
+    solver = _solver(sdir, B)
+    d = _to_dev(s)
+    full = solver.solve_batch(d["xinit"], d["x0"], d["params"])
+    comp = solver.solve_batch(d["xinit"], d["x0"], d["params"][:, 0].contiguous())
+    for k in ("z", "action", "exitflag", "iters", "obj"):
+        assert torch.equal(full[k], comp[k]), k
+    assert float((full["exitflag"] == 1).double().mean()) > 0.99
+    z = torch.empty_like(full["z"])
+    rc = solver.lib.rmpc_solve_batch_strided(solver._h, B, d["xinit"].data_ptr(), d["x0"].data_ptr(), d["params"].data_ptr(),
+                                             solver.N * solver.npar, solver.npar - 1, z.data_ptr(), None, None, None)
+    assert rc != 0 and b"params_stage_stride" in solver.lib.rmpc_last_error()
