@@ -45,7 +45,7 @@ WORKLOADS = {
 # alone with a cold L2), and where it is kept.  A solve is two concurrent launches: solve_kernel<1> (feasible starts,
 # 13.3 ms alone) and solve_kernel<2> (infeasible starts: for this workload it reads every problem once, finds none and
 # exits after 38 us).  Both read the inputs, hence twice the algorithmic bytes when neither finds them in L2.
-NCU_TRAFFIC = {"boxer_radial": ((52.709376e6 + 0.701184e6) + (52.524288e6 + 0.375552e6), "profiles/r1l_ncu_boxer_radial_B4096.txt")}
+NCU_TRAFFIC = {"boxer_radial": ((52.855296e6 + 0.603392e6) + (52.525568e6 + 0.399104e6), "profiles/r1m_ncu_boxer_radial_B4096.txt")}
 
 
 _OUT = None
