@@ -45,6 +45,7 @@ struct rmpc_solver {
   int* counter;       // device work-queue heads, one per in-flight call slot (round robin)
   int counter_slot;
   int blocks_per_sm, blocks_per_sm_sh, sm_count;
+  size_t smem_bytes;  // dynamic shared memory per block
   // the kernel for infeasible starts runs on a side stream, forked from and joined to the caller's stream; a few of
   // them in rotation, so that calls on different streams do not queue behind each other here
   cudaStream_t side[kSideStreams];
@@ -238,7 +239,9 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   };
   if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
   if ((e = cudaMalloc(&s->counter, sizeof(int) * kCounterSlots)) != cudaSuccess) return fail("cudaMalloc", e);
-  const size_t smem = kSharedPerWarp * kWarps;
+  size_t smem = kSharedPerWarp * kWarps;
+  if (const char* pad = getenv("RMPC_PAD_SMEM_KB")) smem += (size_t)atoi(pad) * 1024;  // experiment knob: fewer resident problems per SM
+  s->smem_bytes = smem;
   using I = Ipm<M, double, 32>;
   if ((e = cudaFuncSetAttribute(solve_kernel<I::kFeasible>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(solve_kernel<I::kShifted>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
@@ -322,14 +325,14 @@ int rmpc_solve_batch_strided(rmpc_solver* s, int B, const double* xinit, const d
   CK(cudaStreamWaitEvent(s->side[ss], s->ev_fork[ss], 0));
   long grid = (long)s->blocks_per_sm_sh * s->sm_count;
   if (grid > need) grid = need;
-  solve_kernel<I::kShifted><<<(unsigned)grid, 32 * kWarps, kSharedPerWarp * kWarps, s->side[ss]>>>(B, a, counter + 1);
+  solve_kernel<I::kShifted><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, s->side[ss]>>>(B, a, counter + 1);
   g_launches++;
   CK(cudaGetLastError());
   CK(cudaEventRecord(s->ev_join[ss], s->side[ss]));
   // ... the common case on the caller's stream.  Persistent grid: as many blocks as fit at once, never more than the problems need
   grid = (long)s->blocks_per_sm * s->sm_count;
   if (grid > need) grid = need;
-  solve_kernel<I::kFeasible><<<(unsigned)grid, 32 * kWarps, kSharedPerWarp * kWarps, st>>>(B, a, counter);
+  solve_kernel<I::kFeasible><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, st>>>(B, a, counter);
   CK(cudaStreamWaitEvent(st, s->ev_join[ss], 0));
   g_launches++;
   CK(cudaGetLastError());
