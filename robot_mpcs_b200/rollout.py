@@ -9,10 +9,69 @@ device; nothing leaves the GPU until the summary at the end.
     env.step(action) (pybullet)                                  plant_step(x, u)            (model = plant)
     check_goal_reaching, boxer_example.py:219-224                ||q[:2] - goal|| <= epsilon, per scenario
     per-stage FreeSpaceDecomposition in Python, :191-203         fsd_points=... -> rmpc_fsd_constraints on the previous plan
+    GlobalPlanner.get_local_goal + setGoalReaching,              global_path=LocalGoalPicker(...): waypoint index per
+      boxer_example_supermarket.py:235-237                         scenario kept on the device, goal parameter rewritten per step
 """
 from __future__ import annotations
 
+import math
+
 import torch
+
+
+class LocalGoalPicker:
+    """Batched GlobalPlanner.get_local_goal (robotmpcs/global_planner/globalPlanner.py:174-189, threshold :13): every
+    scenario walks along its own global path; the waypoint index moves on by one when the robot is within
+    `threshold_local_goal` of the current waypoint and the waypoint is not the last.  The A* search that produces the
+    path is out of scope; paths come in as data.
+
+    paths[B, L, 2] (rows beyond a scenario's length are ignored), lengths[B] >= 1; tensors live wherever `paths` does.
+    With B == 1 and a python list/ndarray path, `get_local_goal(position, path)` has the reference's signature."""
+
+    def __init__(self, paths=None, lengths=None, threshold_local_goal: float = 1.3):
+        self.threshold_local_goal = float(threshold_local_goal)
+        self.idx_local = 0
+        self._paths = None
+        if paths is not None:
+            self.set_paths(paths, lengths)
+
+    def set_paths(self, paths, lengths=None):
+        paths = torch.as_tensor(paths, dtype=torch.float64)
+        if paths.ndim == 2:
+            paths = paths[None]
+        B, L = paths.shape[0], paths.shape[1]
+        if lengths is None:
+            lengths = torch.full((B,), L, dtype=torch.int64, device=paths.device)
+        lengths = torch.as_tensor(lengths, dtype=torch.int64, device=paths.device)
+        if L == 0 or bool((lengths < 1).any()) or bool((lengths > L).any()):
+            raise IndexError("every scenario needs a path of 1..L waypoints")  # the reference indexes path[0]: IndexError
+        self._paths, self._lengths = paths[..., :2].contiguous(), lengths
+        self.idx_local = torch.zeros(B, dtype=torch.int64, device=paths.device)
+        return self
+
+    def step(self, position: torch.Tensor) -> torch.Tensor:
+        """position[B, >=2] -> local_goal[B, 2]; advances idx_local in place."""
+        B = self._paths.shape[0]
+        ar = torch.arange(B, device=self._paths.device)
+        wp = self._paths[ar, self.idx_local]
+        d = torch.sqrt((wp[:, 0] - position[:, 0]) ** 2 + (wp[:, 1] - position[:, 1]) ** 2)
+        adv = (self.idx_local < self._lengths - 1) & (d <= self.threshold_local_goal)
+        self.idx_local = self.idx_local + adv.to(torch.int64)
+        return self._paths[ar, self.idx_local]
+
+    def final_goal(self) -> torch.Tensor:
+        ar = torch.arange(self._paths.shape[0], device=self._paths.device)
+        return self._paths[ar, self._lengths - 1]
+
+    def get_local_goal(self, position, path):
+        """Reference-shaped single-scenario call: the path is passed every time, the index is kept by the object."""
+        i = int(self.idx_local[0]) if isinstance(self.idx_local, torch.Tensor) else int(self.idx_local)
+        wp = path[i]                                     # empty path: IndexError, as in the reference (:181)
+        d = math.sqrt((wp[0] - position[0]) ** 2 + (wp[1] - position[1]) ** 2)
+        if i < len(path) - 1 and d <= self.threshold_local_goal:
+            i += 1
+        self.idx_local = i
+        return path[i]
 
 
 def plant_step(x: torch.Tensor, u: torch.Tensor, dt: float, diffdrive: bool, nodes: int = 5) -> torch.Tensor:
@@ -35,11 +94,13 @@ def plant_step(x: torch.Tensor, u: torch.Tensor, dt: float, diffdrive: bool, nod
 
 
 def closed_loop(planner, x0: torch.Tensor, goal: torch.Tensor, steps: int, epsilon: float = 0.2, fsd_points=None,
-                fsd_radius: float = 5.0, on_step=None) -> dict:
+                fsd_radius: float = 5.0, on_step=None, global_path: "LocalGoalPicker | None" = None) -> dict:
     """Runs `steps` control steps for the planner's whole batch.  x0[B,nx], goal[B,>=2] CUDA float64; the planner must
     be device resident with its scenario parameters already set.  fsd_points[B,P,3] switches on the per-step
     free-space decomposition (LinearConstraints models): planes for stage k are seeded from the previous plan's stage
-    k+1 pose, or from the measured pose at the first step, as boxer_example.py:191-201 does."""
+    k+1 pose, or from the measured pose at the first step, as boxer_example.py:191-201 does.  global_path: a
+    LocalGoalPicker on the same device; per step the goal parameter becomes the scenario's current waypoint
+    (boxer_example_supermarket.py:235-237) and `goal` (the final goal) is only used for the reached check."""
     diffdrive = planner._robotType.startswith("boxer")
     dt = planner.dt()
     nx, B = planner._nx, x0.shape[0]
@@ -54,6 +115,8 @@ def closed_loop(planner, x0: torch.Tensor, goal: torch.Tensor, steps: int, epsil
     idx = [planner._paramMap[f"lin_constrs_{i}"][0] for i in range(K)] if fsd_points is not None else None
     z_prev = None
     for t in range(steps):
+        if global_path is not None:
+            planner.setGoalReaching(global_path.step(x[:, :2]))
         if fsd_points is not None:
             if z_prev is None:
                 ref = x[:, :3].contiguous()

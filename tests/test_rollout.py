@@ -54,3 +54,50 @@ def test_point_robot_closed_loop(built):
     it = r["mean_iters"].cpu().numpy()
     assert it[5:].mean() < 0.9 * it[0]                                    # previous-plan warm starts pay off (12.3 -> 10.2)
     assert r["path"].shape == (B, T + 1, 2)
+
+
+def test_point_robot_follows_global_path(built):
+    """Goal switching (boxer_example_supermarket.py:235-237): every scenario has its own 4-waypoint
+    path; per step the goal parameter is the current waypoint.  Properties: the goal written into the parameters is the
+    picker's waypoint, indices only move forward and by one, and scenarios get through their waypoints to the last."""
+    import torch
+    from robot_mpcs_b200.planner.mpcPlanner import MPCPlanner
+    from robot_mpcs_b200.rollout import LocalGoalPicker, closed_loop
+    from robot_mpcs_b200.utils.utils import parse_setup
+    B, T, L = 64, 120, 4
+    setup = parse_setup(os.path.join(CONFIG, "pointRobotMpc.yaml"))["mpc"]
+    setup["initialization"] = "previous_plan"
+    pl = MPCPlanner("pointRobot", SOLVERS + os.sep, batch_size=B, device_resident=True, **setup)
+    pl.concretize()
+    pl.reset()
+    pm = yaml.safe_load(open(os.path.join(SOLVERS, "pointRobot_n3_005_H20_noSlack", "paramMap.yaml")))
+    s = sc.point_robot_sweep(pm, B, seed=9)
+    dev = torch.device("cuda:0")
+    P = torch.as_tensor(s["params"], device=dev)
+    P[:, :, pm["obst"][0]] = 50.0                                         # obstacle parked far away: this test is about goals
+    P[:, :, pm["obst"][1]] = 50.0
+    pl._params3[:] = P
+    x0 = torch.as_tensor(s["xinit"], device=dev)
+    g = torch.Generator().manual_seed(4)
+    steps = torch.rand(B, L, 2, generator=g, dtype=torch.float64) * 1.5 + 0.5
+    steps[..., 1] -= 1.25
+    paths = (x0[:, None, :2].cpu() + torch.cumsum(steps, 1)).to(dev)
+    lengths = torch.randint(2, L + 1, (B,), generator=g).to(dev)
+    picker = LocalGoalPicker(paths, lengths, threshold_local_goal=1.3)
+    gi = pm["goal"]
+    seen = []
+
+    def on_step(t, x, z, flag):
+        ar = torch.arange(B, device=dev)
+        assert torch.equal(pl._params3[:, 0, gi[:2]], paths[ar, picker.idx_local])
+        assert torch.equal(pl._params3[:, -1, gi[:2]], paths[ar, picker.idx_local])
+        seen.append(picker.idx_local.clone())
+
+    r = closed_loop(pl, x0, picker.final_goal(), T, epsilon=0.3, on_step=on_step, global_path=picker)
+    idx = torch.stack(seen)
+    dif = idx[1:] - idx[:-1]
+    assert int(dif.min()) >= 0 and int(dif.max()) <= 1
+    assert bool((idx[-1] == lengths - 1).all())                           # everybody got to the last waypoint ...
+    assert int(r["failures"].sum()) == 0
+    assert float((r["goal_distance"] < 1.0).double().mean()) > 0.9        # ... and is at it (or has been: `reached`)
+    assert float(r["reached"].double().mean()) > 0.8
