@@ -210,7 +210,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from robot_mpcs_b200.planner.solver import Solver
-    from robot_mpcs_b200.parallel import gather_results
+    from robot_mpcs_b200.parallel import gather_results, init_process_group
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -220,7 +220,7 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        init_process_group("nccl", device_id=dev)   # one NCCL channel: see robot_mpcs_b200/parallel.py
     sdir, _, defB, f_iter, desc = WORKLOADS[args.workload]
     B = args.batch or defB
     solver = Solver.from_directory(os.path.join(SOLVERS, sdir), device=local_rank, max_batch=B)
