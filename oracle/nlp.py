@@ -243,6 +243,36 @@ class OracleModel:
             rows += self._module_rows(c, z, p)
         return torch.stack(rows, -1)
 
+    LIMIT_MODULES = ("JointLimitConstraints", "InputLimitConstraints", "VelLimitConstraints")
+
+    def ineq_general(self, z, p) -> torch.Tensor:
+        """The rows of h that are not simple bounds on one variable (Radial, Linear, SelfCollision), in h order."""
+        rows = []
+        for c in self.constraints:
+            if c not in self.LIMIT_MODULES:
+                rows += self._module_rows(c, z, p)
+        return torch.stack(rows, -1) if rows else torch.zeros(z.shape[:-1] + (0,), dtype=DT)
+
+    def simple_bounds(self, P):
+        """(lo, hi)[N, nvar]: the limit rows `z_j - lo_j >= 0`, `hi_j - z_j >= 0` of JointLimit / InputLimit / VelLimit
+        (inequalities/{JointLimit,InputLimit,VelLimit}Constraints.py) intersected with the +-100 box of
+        models/mpcModel.py:23-28,98-104 — the same feasible set, stated as bounds for solvers that treat bounds cheaply."""
+        N = P.shape[0]
+        lo = torch.full((N, self.nvar), -100.0, dtype=DT)
+        hi = torch.full((N, self.nvar), 100.0, dtype=DT)
+        for c in self.constraints:
+            if c == "JointLimitConstraints":
+                sl, names = slice(0, self.n), ("lower_limits", "upper_limits")
+            elif c == "InputLimitConstraints":
+                sl, names = slice(self.nx, self.nx + self.nu), ("lower_limits_u", "upper_limits_u")
+            elif c == "VelLimitConstraints":
+                sl, names = slice(self.nx - 2, self.nx), ("lower_limits_vel", "upper_limits_vel")
+            else:
+                continue
+            lo[:, sl] = torch.maximum(lo[:, sl], self._P(P, names[0]))
+            hi[:, sl] = torch.minimum(hi[:, sl], self._P(P, names[1]))
+        return lo, hi
+
     def stage_cost(self, z, p) -> torch.Tensor:
         """J(z_k, p_k) (ObjectiveManager.py:28-46): modules + u' diag(wu) u."""
         J = torch.zeros(z.shape[:-1], dtype=DT)
@@ -255,7 +285,10 @@ class OracleModel:
                 for i, c in enumerate(self.constraints):
                     rows = self._module_rows(c, z, p)
                     if rows:
-                        J = J + self.N * w[..., i] / rows[0]
+                        # a zero weight switches the term off (all shipped configs but one module): evaluated as 0, not
+                        # as 0/h, which is NaN when a bound-constrained solver puts the row exactly on h = 0
+                        wi = w[..., i]
+                        J = J + self.N * wi / torch.where(wi == 0, torch.ones_like(rows[0]), rows[0])
         u = z[..., self.nx:]
         return J + (self._P(p, "wu") * u * u).sum(-1)
 

@@ -45,13 +45,14 @@ struct Options {
   double gn_hold_max;                       // longest run of iterations that skip the exact-Hessian attempt after it failed (0: always try)
   double stall_window;                      // give up (-7) when the optimality error has not dropped 10x within this many iterations (0 = never)
   double creep_trigger, creep_factor;      // consecutive boundary-cut full steps that trigger a barrier increase, and its factor
+  double ls_optimistic;                     // 1: the first trial step is capped by the (linear) limit rows only; the nonlinear rows are checked on their true values
 };
 
 RMPC_HD Options default_options() {
   Options o;
   o.max_iter = 200; o.hessian = 1;
   o.tol_stat = 1e-6; o.tol_eq = 1e-8; o.tol_ineq = 1e-8; o.tol_comp = 1e-8;
-  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3; o.creep_trigger = 3; o.creep_factor = 10; o.stall_window = 0; o.gn_hold_max = 4;
+  o.mu0 = 1.0; o.mu_min = 1e-9; o.reg = 0.0; o.delta = 1e-2; o.kappa = 1e10; o.tau_min = 0.99; o.lm0 = 1e-2; o.lm_up = 4.0; o.lm_down = 0.25; o.lm_trigger = 3; o.creep_trigger = 3; o.creep_factor = 10; o.stall_window = 0; o.gn_hold_max = 4; o.ls_optimistic = 0;
   return o;
 }
 
@@ -523,6 +524,12 @@ struct Ipm {
     g.sync();
   }
 
+  static constexpr RMPC_HD bool row_is_geo(int r) {
+    for (int i = 0; i < M::NGEO; ++i)
+      if (M::geo_row(i) == r) return true;
+    return false;
+  }
+
   RMPC_HD void row_dirs(int sl, int k, T* gd) const {
     const T* sdz = S.st[k].dz;
     RMPC_UNROLL
@@ -666,7 +673,7 @@ struct Ipm {
       rollout(mu);
       const T tau = tmax(T(opt.tau_min), T(1) - mu);
       const T mu_est = mu;
-      float rp = 0.0f, rd = 0.0f;  // step-length caps: single precision is enough (the true rows are checked in the line search)
+      float rp = 0.0f, rpl = 0.0f, rd = 0.0f;  // step-length caps: single precision is enough (the true rows are checked in the line search)
       T dphi = T(0);
       RMPC_UNROLL
       for (int sl = 0; sl < SLOTS; ++sl) {
@@ -685,6 +692,7 @@ struct Ipm {
             if constexpr (SH) dphi += (lr * rs) * shr * gd[r];   // g0 holds the cost gradient minus the shift push: undo it here
             const T dlr = mu * rs - lr - (lr * rs) * dsr;
             rp = fmaxf(rp, float(-dsr * rs));             // largest relative decrease of a slack ...
+            if (!row_is_geo(r)) rpl = fmaxf(rpl, float(-dsr * rs));   // ... and of the slack of a limit row (linear: its estimate is exact)
             S.st[k].Qs[NH + r] = dlr;                     // kept for the multiplier update (K, kff and g0 are dead from here on)
             rd = fmaxf(rd, fdiv_approx(-float(dlr), float(lr)));      // ... and of a multiplier, for the fraction-to-boundary rule
             dphi -= mu * dsr * rs;
@@ -693,6 +701,12 @@ struct Ipm {
       }
       rp = g.max(rp); rd = g.max(rd); dphi = g.sum(dphi);
       const T ap = T(rp) > tau ? tau / T(rp) : T(1), ad = T(rd) > tau ? tau / T(rd) : T(1);
+      // The slack of a row is the row's own value here, s = h(z) + shift, so only the true rows have to stay inside.  The
+      // geometric rows are convex in the point they constrain (distances), their linearisation underestimates them, and
+      // a cap taken from it makes the iterate crawl along a curved obstacle: the first trial is capped by the limit rows
+      // only, and falls back to the linearised cap when a true row objects.
+      T ap0 = ap;
+      if (opt.ls_optimistic > 0) { rpl = g.max(rpl); ap0 = T(rpl) > tau ? tau / T(rpl) : T(1); }
       if (so.theta > T(1e-14)) {
         const T need = dphi * trcp(T(0.9) * so.theta);
         if (need > rho_pen) rho_pen = need * T(1.1) + T(1e-3);
@@ -700,10 +714,11 @@ struct Ipm {
       const T phi0 = so.f - mu * so.logs + rho_pen * so.theta;
       const T slope = dphi - rho_pen * so.theta;
       // ---- backtracking: stay inside h + shift >= (1 - tau) s on the true rows, Armijo on the l1 merit
-      T alpha = ap;
+      T alpha = ap0;
       bool accepted = false;
       int nls = 0;
-      bool cut = false;  // the first trial left the interior of a nonlinear row
+      bool cut = false;  // the first trial within the linearised cap left the interior of a nonlinear row
+      bool lin_tried = false;
       for (int ls = 0; ls < 30; ++ls) {
         T f = T(0), theta = T(0);
         LogAcc<T> la;
@@ -755,8 +770,13 @@ struct Ipm {
         if (RMPC_TRACE > 1) printf("    ls %d alpha %.3g f %.9g (f0 %.9g) theta %.4g (%.4g) barrier %.6g (%.6g) bad %d phi-phi0 %.4g\n", ls, double(alpha), double(f), double(so.f), double(theta), double(so.theta), double(-mu * logs), double(-mu * so.logs), int(bad), double(phi - phi0));
 #endif
         if (!bad && (phi == phi) && phi <= phi0 + T(1e-4) * alpha * slope + tol_phi) { accepted = true; break; }
+        if (alpha > ap) {   // an optimistic trial beyond the linearised cap: not counted as a backtrack
+          alpha = bad ? tmin(ap, T(0.5) * alpha) : T(0.5) * alpha;
+          continue;
+        }
         alpha *= T(0.5);
-        if (ls == 0 && bad) cut = true;
+        if (!lin_tried && bad) cut = true;
+        lin_tried = true;
         ++nls;
       }
 #if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)

@@ -152,6 +152,69 @@ def boxer_supermarket(pmap, B, N=40, npar=55, K=8, seed=2):
     return {"xinit": xinit, "x0": x0, "params": P}
 
 
+def boxer_linear(pmap, B, N=10, npar=27, seed=5):
+    """The reference's shipped boxer config (config/boxerMpc.yaml: N=10, one half-plane from LinearConstraints, K=1): the
+    plane is the same for every stage of a scenario here (examples/boxer_example.py:93 uses one filler plane); the start
+    ee point sits U(0.8, 2.0) on its positive side and the goal U(1, 3) away in a random direction, so the plane is
+    active for roughly a third of the scenarios."""
+    g = _rng(seed)
+    xinit = _boxer_start(g, B)
+    ee = xinit[:, :2] + 0.4 * np.stack([np.cos(xinit[:, 2]), np.sin(xinit[:, 2])], 1)
+    ang = g.uniform(0, 2 * math.pi, (B, 1))
+    goal = xinit[:, :2] + g.uniform(1, 3, (B, 1)) * np.concatenate([np.cos(ang), np.sin(ang)], 1)
+    P = np.zeros((B, N, npar))
+    _boxer_common(P, pmap, B)
+    _fill(P, pmap, "goal", np.concatenate([goal, np.zeros((B, 1))], 1))
+    a = g.uniform(0, 2 * math.pi, (B, 1))
+    nrm = np.concatenate([np.cos(a), np.sin(a)], 1)
+    clear = g.uniform(0.8, 2.0, (B, 1))
+    d0 = clear - (nrm * ee).sum(1, keepdims=True)
+    _fill(P, pmap, "lin_constrs_0", np.concatenate([nrm, np.zeros((B, 1)), d0], 1))
+    x0 = np.zeros((B, N, 10))
+    x0[:, :, :8] = xinit[:, None, :]
+    return {"xinit": xinit, "x0": x0, "params": P}
+
+
+def boxer_vel(pmap, B, N=15, npar=36, K=2, seed=7):
+    """config/boxerVelMpc.yaml: boxer with VelLimitConstraints on (v, omega) (inequalities/VelLimitConstraints.py:19-31) and
+    control_mode vel (planner/mpcPlanner.py:275-278).  Goal 3-5 m away, forward speed limited to 1 m/s and turn rate to
+    1 rad/s, so both velocity limits become active; two sphere obstacles as in boxer_radial."""
+    g = _rng(seed)
+    xinit = _boxer_start(g, B)
+    ee = xinit[:, :2] + 0.4 * np.stack([np.cos(xinit[:, 2]), np.sin(xinit[:, 2])], 1)
+    ang = g.uniform(0, 2 * math.pi, (B, 1))
+    goal = xinit[:, :2] + g.uniform(3, 5, (B, 1)) * np.concatenate([np.cos(ang), np.sin(ang)], 1)
+    obst = np.zeros((B, K, 4))
+    for k in range(K):
+        c = ee + g.uniform(-4, 4, (B, 2))
+        r = g.uniform(0.2, 0.6, (B,))
+        for _ in range(50):
+            bad = np.linalg.norm(c - ee, axis=1) - r - 0.6 < 0.2
+            if not bad.any():
+                break
+            c[bad] = ee[bad] + g.uniform(-4, 4, (int(bad.sum()), 2))
+        bad = np.linalg.norm(c - ee, axis=1) - r - 0.6 < 0.2
+        c[bad] = np.array([50.0, 50.0])
+        obst[:, k, :2] = c
+        obst[:, k, 3] = r
+    P = np.zeros((B, N, npar))
+    _fill(P, pmap, "r_body", [0.6])
+    _fill(P, pmap, "obst", obst.reshape(B, 4 * K))
+    _fill(P, pmap, "lower_limits", [-10.0] * 3)
+    _fill(P, pmap, "upper_limits", [10.0] * 3)
+    _fill(P, pmap, "lower_limits_u", [-10.0] * 2)
+    _fill(P, pmap, "upper_limits_u", [10.0] * 2)
+    _fill(P, pmap, "lower_limits_vel", [-0.3, -1.0])
+    _fill(P, pmap, "upper_limits_vel", [1.0, 1.0])
+    _fill(P, pmap, "wu", [0.01] * 2)
+    _fill(P, pmap, "goal", np.concatenate([goal, np.zeros((B, 1))], 1))
+    _fill(P, pmap, "wgoal", [1.0] * 3)
+    _fill(P, pmap, "wconstr", [0.0] * 5)
+    x0 = np.zeros((B, N, 10))
+    x0[:, :, :8] = xinit[:, None, :]
+    return {"xinit": xinit, "x0": x0, "params": P}
+
+
 PANDA_LIMITS = np.array([[-2.8973, 2.8973], [-1.7628, 1.7628], [-2.8973, 2.8973], [-3.0718, -0.0698],
                          [-2.8973, 2.8973], [-0.0175, 3.7525], [-2.8973, 2.8973]])
 PANDA_LIMITS_U = np.array([[-1, 1], [-1, 1], [-15, 15], [-15, 15], [-7.5, 7.5], [-10, 10], [-12.5, 12.5]], dtype=np.float64)

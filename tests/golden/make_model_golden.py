@@ -31,7 +31,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 CONFIG = os.path.join(ROOT, "robot_mpcs_b200", "config")
 ASSETS = os.path.join(ROOT, "robot_mpcs_b200", "assets")
-CASES = ["pointRobotMpc.yaml", "boxerRadialMpc.yaml", "pandaMpc.yaml", "boxerSupermarketMpc.yaml", "boxerMpc.yaml"]
+CASES = ["pointRobotMpc.yaml", "boxerRadialMpc.yaml", "pandaMpc.yaml", "boxerSupermarketMpc.yaml", "boxerMpc.yaml",
+         "boxerVelMpc.yaml"]   # the last one instantiates VelLimitConstraints (no shipped config of the reference does)
 
 
 class V(np.ndarray):
