@@ -17,7 +17,15 @@
  * (message via rmpc_last_error()).  Per-problem solver status is reported only through info.exitflag[]
  * with the FORCESPRO sign convention the reference tests (mpcPlanner.py:263): 1 optimal, 0 iteration limit,
  * <0 failure (-5 factorisation, -6 NaN/Inf, -7 no progress / locally infeasible, -8 initial guess on the wrong side
- * of a ConstraintAvoidance pole).
+ * of a ConstraintAvoidance pole, -9 the converged point touches or leaves the -100 <= z <= 100 box of the reference's NLP
+ * (models/mpcModel.py:23-28,98-104), which this solver checks but does not carry as rows: not a solution of that NLP;
+ * -1 the problem was never written: an internal error).
+ *
+ * Threading: a handle may be driven from several host threads and on any mix of streams; the host side of every entry
+ * point is serialised per handle by a mutex, the launches themselves are asynchronous.  Up to 8 batched solves of one
+ * handle can be in flight at a time on different streams (each owns one of 8 slots of queue heads and problem lists);
+ * the ninth waits, in stream order and without blocking the host, for the first to finish.  Every entry point runs on
+ * the handle's device and restores the calling thread's current device before it returns.
  */
 #ifndef RMPC_H
 #define RMPC_H
@@ -70,8 +78,12 @@ int rmpc_set_options(rmpc_solver* s, const rmpc_options* opt);
 int rmpc_get_options(const rmpc_solver* s, rmpc_options* out);
 
 /* Solve B problems.  All array arguments are DEVICE pointers owned by the caller; the call is asynchronous
- * on `stream` (a cudaStream_t passed as void*, NULL = default stream).  z_out / action_out / info may be NULL.
- * One kernel launch (one warp per problem, persistent grid with a device work queue) after a 4-byte memset. */
+ * on `stream` (a cudaStream_t passed as void*, NULL = default stream).  z_out / action_out / info may be NULL; z_out may
+ * alias x0 (every problem's guess is read by the one kernel that then writes its plan).
+ * Launches: a 16-byte memset of the call's queue slot, classify_kernel (every problem is classified once: does a row of
+ * its initial guess start infeasible? -> two index lists), then two persistent solve kernels side by side (one warp per
+ * problem, each pulling from its own list): feasible starts on `stream`, infeasible starts on a side stream forked from
+ * and joined to it.  B <= 32 takes a single launch that classifies inside the solve. */
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
                      double* z_out, double* action_out, const rmpc_info* info, void* stream);
 
@@ -98,15 +110,25 @@ int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, cons
 int rmpc_wait(rmpc_solver* s);
 
 /* Warm start for `initialization: previous_plan` (mpcPlanner.py:215-226 shiftHorizon): x0[b][k] = z[b][k+1] for
- * k < N-1, x0[b][N-1] = z[b][N-1].  Device pointers, [B][N][nvar] each; in-place (x0 == z) is allowed. */
+ * k < N-1, x0[b][N-1] = z[b][N-1].  Device pointers, [B][N][nvar] each; in-place (x0 == z) is allowed (one thread walks
+ * the horizon of one variable, no scratch copy). */
 int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void* stream);
 
 /* Batched parameter scatter (the set* loops of mpcPlanner.py:120-210): for every problem b and every stage k,
  * params[b][k][idx[j]] = values[b][j] (stage_varying == 0, values is [B][n_idx]) or values[b][k][j]
- * (stage_varying == 1, values is [B][N][n_idx]).  idx is a HOST array of paramMap indices; the rest are device
- * pointers. */
+ * (stage_varying == 1, values is [B][N][n_idx]).  idx is a HOST array of paramMap indices (it travels by value with
+ * the launch); the rest are device pointers. */
 int rmpc_set_params(rmpc_solver* s, int B, double* params, const int* idx, int n_idx, const double* values,
                     int stage_varying, void* stream);
+
+/* Constant-acceleration prediction of moving obstacles over the horizon (planner/mpcPlanner.py:144-161
+ * updateDynamicObstacles): obst_state[B][n_dyn][9] = (position, velocity, acceleration) of each moving obstacle; for every
+ * problem, stage k and obstacle slot j < n_slots (= number_obstacles) the parameters
+ * params[b][k][p_obst + 4 j .. + 3] become (pos + vel (k dt) + acc (k dt)^2 / 2, radius) for j < n_dyn and
+ * (-100, -100, -100, radius) otherwise (mpcPlanner.py:152-154,158-160; `radius` is the reference's self._r).  p_obst is
+ * paramMap["obst"][0].  Device pointers, asynchronous on `stream`. */
+int rmpc_predict_obstacles(rmpc_solver* s, int B, const double* obst_state, int n_dyn, int n_slots, int p_obst, double radius,
+                           double* params, void* stream);
 
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py reports it). */
 long rmpc_launch_count(void);

@@ -553,20 +553,44 @@ struct Ipm {
   // ---- the solve ----------------------------------------------------------------------------------
   // The iteration exists twice: iterate<true> knows about rows that start infeasible (shifted rows), iterate<false>
   // does not and is smaller and cheaper in registers.  MODE picks what a build of solve() contains:
-  //   kAll      every problem (the CPU twin)
-  //   kFeasible only problems whose initial guess satisfies every row with margin delta: no shift code at all; returns
-  //             false, outputs untouched, for the others
-  //   kShifted  only the others; returns false for a problem kFeasible takes
-  // The CUDA host code runs the last two as two kernels side by side, so that the common case runs the smaller code.
+  //   kAll      every problem; decides by itself which copy a problem needs (the CPU twin, and the single-launch
+  //             kernel for small batches)
+  //   kFeasible problems that starts_shifted() found feasible: no shift code at all
+  //   kShifted  the others: iterate<true> until the last shift is gone, then iterate<false>
+  // The CUDA host code classifies a batch ONCE (classify_kernel -> two index lists) and runs the last two as two
+  // kernels side by side, each on its own list, so that the common case runs the smaller code.
   static constexpr int kAll = 0, kFeasible = 1, kShifted = 2;
-  template <int MODE = 0>
-  RMPC_HD bool solve(const T* xinit, const T* z_in, T* z_out, Info& info) {
-    // initial point: z from the guess, x_1 = xinit
+
+  RMPC_HD void load_guess(const T* xinit, const T* z_in) {
     for (int e = g.lane; e < N * NV; e += G) S.st[e / NV].z[e % NV] = z_in[e];
     g.sync();
     for (int e = g.lane; e < NX; e += G) S.st[0].z[e] = xinit[e];
     for (int e = g.lane; e < N; e += G) { S.st[e].nu01[0] = T(0); S.st[e].nu01[1] = T(0); }
     g.sync();
+  }
+
+  // Does a row of the loaded initial guess start below delta?  (the one place a problem is classified on the GPU path)
+  RMPC_HD bool starts_shifted() {
+    bool shifted = false;
+    RMPC_UNROLL
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      const int k = g.lane + G * sl;
+      if (k < N) {
+        T p[M::NPAR];
+        load_params<M, T>(pv, k, p);
+        StageVal<M, T> sv;
+        stage_values<M, T>(S.st[k].z, p, sv);
+        RMPC_UNROLL
+        for (int r = 0; r < NH; ++r) shifted = shifted || !(sv.h[r] >= T(opt.delta));
+      }
+    }
+    return g.any(shifted);
+  }
+
+  template <int MODE = 0>
+  RMPC_HD void solve(const T* xinit, const T* z_in, T* z_out, Info& info) {
+    // initial point: z from the guess, x_1 = xinit
+    load_guess(xinit, z_in);
     T mu = T(opt.mu0);
     bool pole0 = false, shifted = false;
     RMPC_UNROLL
@@ -582,10 +606,14 @@ struct Ipm {
         for (int r = 0; r < NH; ++r) {
           const T hv = sv.h[r];
           // a violated row starts with a slack as large as its violation: the fraction-to-boundary rule then leaves room
-          // for steps that remove only part of the shift
-          const float shift = hv >= T(opt.delta) ? 0.0f : float(tmax(T(opt.delta), -hv) - hv);
-          if constexpr (MODE != kFeasible) sh[sl][r] = shift;
-          shifted = shifted || shift > 0.0f;
+          // for steps that remove only part of the shift.  kFeasible: the classification found every row >= delta, and
+          // the row is taken as it is (no shift storage in that build).
+          float shift = 0.0f;
+          if constexpr (MODE != kFeasible) {
+            shift = hv >= T(opt.delta) ? 0.0f : float(tmax(T(opt.delta), -hv) - hv);
+            sh[sl][r] = shift;
+            shifted = shifted || shift > 0.0f;
+          }
           s[sl][r] = hv + T(shift);
           lam[sl][r] = mu * trcp(hv + T(shift));
         }
@@ -600,13 +628,11 @@ struct Ipm {
     // costs registers and instructions in every unrolled row loop: the iteration exists twice, and the copy that
     // knows about shifts runs only until the last shift of the problem has reached zero.
     bool done = false;
-    if (g.any(shifted)) {
-      if constexpr (MODE != kFeasible) done = iterate<true>(L, info);
-      else return false;
-    } else if (MODE == kShifted) return false;
+    if constexpr (MODE != kFeasible) {
+      if (MODE == kShifted || g.any(shifted)) done = iterate<true>(L, info);
+    }
     if (!done) iterate<false>(L, info);
     finish(L, z_out, info);
-    return true;
   }
 
 
@@ -839,6 +865,15 @@ struct Ipm {
   RMPC_HD void finish(const Loop& L, T* z_out, Info& info) {
     if (z_out)
       for (int e = g.lane; e < N * NV; e += G) z_out[e] = S.st[e / NV].z[e % NV];
+    // The NLP of the reference carries -100 <= z <= 100 on every stage variable (models/mpcModel.py:23-28,98-104).  The
+    // box is not part of the barrier problem solved here (it is never active in a sensible scenario, and 2 nvar more rows
+    // per stage would cost every solve); a converged point that touches or leaves it is not a solution of the
+    // reference's NLP and is reported as such (exit flag -9) instead of as optimal.
+    if (info.exitflag == 1) {
+      float zmax = 0.0f;
+      for (int e = g.lane; e < N * NV; e += G) zmax = fmaxf(zmax, float(tabs(S.st[e / NV].z[e % NV])));
+      if (g.max(zmax) > 100.0f - 1e-4f) info.exitflag = -9;
+    }
     info.iters = L.it > opt.max_iter ? opt.max_iter : L.it;
     info.obj = double(L.so.f);
     info.res_stat = double(L.so.res_stat);

@@ -11,6 +11,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <atomic>
+#include <mutex>
 
 #include "model_traits.h"
 #ifndef RMPC_WARPS_FIXED
@@ -36,50 +37,72 @@ static std::atomic<long> g_launches{0};
     }                                                                                              \
   } while (0)
 
-constexpr int kSideStreams = 4;
+// Every entry point runs on the handle's device and leaves the calling thread's current device as it found it.
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err;
+  explicit DeviceGuard(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+    else if (err == cudaSuccess) prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define GUARD(s) DeviceGuard guard_((s)->device); CK(guard_.err)
+
+// Calls in flight per handle (on any mix of streams): each call owns one slot = queue heads + the two problem lists of
+// its batch + a side stream; a slot is reused only after the call that used it last has finished (stream-ordered wait
+// on the slot's event, no host blocking).
+constexpr int kSlots = 8;
+constexpr int kSmallBatch = 32;     // up to here a batch goes through the single-launch kernel (no classification pass)
+constexpr int kMaxIdx = 128;        // parameter indices per rmpc_set_params launch (passed by value)
+
+struct Slot {
+  int* q;               // device: [0] feasible count, [1] shifted count, [2] feasible head, [3] shifted head
+  int* list;            // device: [max_batch] feasible problems, [max_batch] shifted problems
+  cudaStream_t side;    // the kernel for shifted starts runs here, forked from and joined to the caller's stream
+  cudaEvent_t ev_fork, ev_join, ev_done;
+  bool used;
+};
+
+struct LatencyGraph {   // captured H2D -> single-launch solve -> D2H for one small batch size (rmpc_solve_batch_host)
+  cudaGraphExec_t exec;
+  int B, flags;
+};
 
 struct rmpc_solver {
   int device;
   int max_batch;
   rmpc_options opt;
-  int* counter;       // device work-queue heads, one per in-flight call slot (round robin)
-  int counter_slot;
-  int blocks_per_sm, blocks_per_sm_sh, sm_count;
+  std::mutex mu;        // serialises the host side of every entry point of this handle (launches are asynchronous)
+  Slot slot[kSlots];
+  int next_slot;
+  int blocks_per_sm, blocks_per_sm_sh, blocks_per_sm_all, sm_count;
   size_t smem_bytes;  // dynamic shared memory per block
-  // the kernel for infeasible starts runs on a side stream, forked from and joined to the caller's stream; a few of
-  // them in rotation, so that calls on different streams do not queue behind each other here
-  cudaStream_t side[kSideStreams];
-  cudaEvent_t ev_fork[kSideStreams], ev_join[kSideStreams];
-  int side_slot;
-  double* z_tmp;      // scratch plan for the in-place horizon shift
-  int* d_idx;         // scratch for rmpc_set_params
-  int d_idx_cap;
-  // device staging for the host entry point
-  double *h_xinit, *h_x0, *h_params, *h_z, *h_action, *h_res;
-  int* h_flag;
+  // device staging for the host entry points: one packed input block and one packed output block
+  double* d_in;         // xinit | x0 | params
+  double* d_out;        // z | action | obj res_stat res_eq res_ineq res_comp | exitflag iters (ints)
+  double *p_in, *p_out; // page-locked mirrors
+  bool staged;
   cudaStream_t hstream;  // private stream of the host entry points
-  // page-locked landing zone of the asynchronous D2H copies, and the caller's buffers they are handed to in rmpc_wait
-  double *p_z, *p_action, *p_res;
-  int* p_flag;
   int pend_B;
   double *u_z, *u_action;
   rmpc_info u_info;
+  LatencyGraph lg;
+  int* lat_q;           // queue head of the captured small-batch launch
 };
-
 // ---------------------------------------------------------------------------------------------
 // One warp = one NLP (rmpc_ipm.cuh, G = 32): lane k owns stage k in the stage-parallel phases, the 32 lanes share the
 // per-stage dense algebra of the Riccati sweep through the warp's slice of shared memory.  Warps pull problems from a
-// device-side counter, so a hard problem (many iterations) only delays its own warp.  Inputs and outputs are read and
+// device-side queue, so a hard problem (many iterations) only delays its own warp.  Inputs and outputs are read and
 // written in the reference's own layout ([B][N][nvar], [B][N][npar]); there is no separate pack/unpack pass.
 using Shared = ProblemShared<M, double>;
+using I32 = Ipm<M, double, 32>;
 constexpr size_t kSharedPerWarp = (sizeof(Shared) + 15) / 16 * 16;
 // Warps (= problems) per thread block.  With more than one, the warps of a block meet at the top of every solver
 // iteration (Group<32>::align) so that they walk through the same code together and share instruction-cache fills.
 // Measured on B200 (boxer, 20 steps): 1 warp/block 702 k solves/s, 2: 622 k, 3: 574 k, 7: 534 k — waiting for the
 // slowest iteration of the block costs more than the shared fetches save, so the default stays at 1.
-#ifndef RMPC_WARPS_FIXED
-#define RMPC_WARPS_FIXED 1
-#endif
 constexpr int kWarps = RMPC_WARPS_FIXED;
 static_assert(kWarps >= 1, "one problem does not fit into the shared memory of an SM");
 
@@ -112,21 +135,64 @@ __device__ __forceinline__ void write_outputs(const SolveArgs& a, const Shared& 
   }
 }
 
-// Two instantiations, launched side by side on two streams.  kFeasible is the common case and contains no code for
-// rows that start infeasible; kShifted carries both copies of the iteration and solves only problems whose initial guess
-// violates a row (for a feasible batch it evaluates each problem's rows once and exits).  Each problem is solved and
-// written by exactly one of the two.  With the rare path in the same kernel as the hot one the solver was 4-10 %
-// slower (inlined) or 25 % slower (as a called function); B200, r1l A/B in DESIGN.md.
+// Pass 1 of a batched solve: every problem is classified ONCE — does a row of its initial guess start below delta? —
+// and appended to the list of the kernel that will solve it.  One warp per problem (lane = stage, as in the solve), no
+// shared memory.  Everything after this pass reads a problem's inputs only from the kernel that owns it, and before that
+// kernel writes the problem's outputs, so z_out may alias x0.
+__global__ void __launch_bounds__(256) classify_kernel(int B, const __grid_constant__ SolveArgs a, int* __restrict__ q,
+                                                       int* __restrict__ list, int max_batch) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+    const ParamView<double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
+    bool shifted = false;
+#pragma unroll
+    for (int sl = 0; sl < I32::SLOTS; ++sl) {
+      const int k = lane + 32 * sl;
+      if (k < M::N) {
+        double z[M::NVAR], p[M::NPAR];
+        const double* zin = a.x0 + ((size_t)b * M::N + k) * M::NVAR;
+#pragma unroll
+        for (int i = 0; i < M::NVAR; ++i) z[i] = zin[i];
+        if (k == 0) {
+#pragma unroll
+          for (int i = 0; i < M::NX; ++i) z[i] = a.xinit[(size_t)b * M::NX + i];
+        }
+        load_params<M, double>(pv, k, p);
+        StageVal<M, double> sv;
+        stage_values<M, double>(z, p, sv);
+#pragma unroll
+        for (int r = 0; r < M::NH; ++r) shifted = shifted || !(sv.h[r] >= a.opt.delta);
+      }
+    }
+    shifted = __any_sync(0xffffffffu, shifted) != 0;
+    if (lane == 0) {
+      const int at = atomicAdd(q + (shifted ? 1 : 0), 1);
+      list[(shifted ? max_batch : 0) + at] = b;
+    }
+  }
+}
+
+// Pass 2, two instantiations launched side by side on two streams.  kFeasible is the common case and contains no code for
+// rows that start infeasible; kShifted carries both copies of the iteration and solves the problems of the second list.
+// With the rare path in the same kernel as the hot one the solver was 4-10 % slower (inlined) or 25 % slower (as a called
+// function); B200, r1l A/B in DESIGN.md.  kAll (list == nullptr) is the single-launch form for small batches: it
+// classifies inside the solve and takes problems 0 .. B-1 straight from the queue head.
 template <int MODE>
 __global__ void __launch_bounds__(32 * kWarps, RMPC_MIN_BLOCKS)
-solve_kernel(int B, const __grid_constant__ SolveArgs a, int* __restrict__ counter) {
+solve_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__ list, const int* __restrict__ count,
+             int* __restrict__ head) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5;
   Shared& S = *reinterpret_cast<Shared*>(smem_raw + warp * kSharedPerWarp);
   Group<32> g{int(threadIdx.x & 31)};
+  const int n = MODE == I32::kAll ? B : *count;
   for (;;) {
     int b = 0;
-    if (g.lane == 0) b = atomicAdd(counter, 1);
+    if (g.lane == 0) {
+      b = atomicAdd(head, 1);
+      if (MODE != I32::kAll) b = b < n ? list[b] : B;
+    }
     b = __shfl_sync(0xffffffffu, b, 0);
     if (b >= B) {
       // out of work: keep meeting the other warps of the block at their iteration rendezvous until all are out of work
@@ -135,40 +201,69 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, int* __restrict__ count
     }
     const ParamView<double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
     Info inf;
-    bool mine;
     {
-      Ipm<M, double, 32> ipm(g, S, pv, a.opt);
-      mine = ipm.template solve<MODE>(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR,
-                                      a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
+      I32 ipm(g, S, pv, a.opt);
+      ipm.template solve<MODE>(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR,
+                               a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
     }
-    if (mine) write_outputs(a, S, g.lane, b, inf);
+    write_outputs(a, S, g.lane, b, inf);
     __syncwarp();
   }
 }
 
+// previous-plan warm start, safe in place: one thread per (problem, variable) walks the horizon, reading stage k+1 before
+// anything writes it
 __global__ void shift_kernel(long total, const double* __restrict__ z, double* __restrict__ x0) {
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  const int per = M::N * M::NVAR;
-  const long b = i / per;
-  const int r = int(i - b * per);
-  const int k = r / M::NVAR;
-  const int ks = k < M::N - 1 ? k + 1 : k;
-  // in-place safe: element (k) reads (k+1) which no other thread writes before ... so stage through a register and
-  // rely on one thread per element reading strictly-later data only; x0 == z aliasing is handled by the host (copy).
-  x0[i] = z[b * per + (long)ks * M::NVAR + (r - k * M::NVAR)];
+  const long b = i / M::NVAR;
+  const int v = int(i - b * M::NVAR);
+  const double* src = z + b * M::N * M::NVAR + v;
+  double* dst = x0 + b * M::N * M::NVAR + v;
+  double nxt = src[0];
+#pragma unroll 4
+  for (int k = 0; k < M::N - 1; ++k) {
+    nxt = src[(k + 1) * M::NVAR];
+    dst[k * M::NVAR] = nxt;
+  }
+  dst[(M::N - 1) * M::NVAR] = nxt;
 }
 
-__global__ void scatter_kernel(int B, int n_idx, int stage_varying, const int* __restrict__ idx,
+struct IdxList { int n; int v[kMaxIdx]; };
+
+__global__ void scatter_kernel(int B, int n_all, int off, int stage_varying, const __grid_constant__ IdxList idx,
                                const double* __restrict__ values, double* __restrict__ params) {
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long total = (long)B * M::N * n_idx;
+  const long total = (long)B * M::N * idx.n;
   if (i >= total) return;
-  const int j = int(i % n_idx);
-  const long bk = i / n_idx;
+  const int j = int(i % idx.n);
+  const long bk = i / idx.n;
   const long b = bk / M::N;
-  const double v = stage_varying ? values[i] : values[b * n_idx + j];
-  params[bk * M::NPAR + idx[j]] = v;
+  const double v = stage_varying ? values[bk * n_all + off + j] : values[b * n_all + off + j];
+  params[bk * M::NPAR + idx.v[j]] = v;
+}
+
+// Constant-acceleration prediction of the moving obstacles over the horizon, written into the stage-varying `obst`
+// parameter slots (planner/mpcPlanner.py:144-161): stage i sees pos + vel (i dt) + acc (i dt)^2 / 2, radius r; obstacle
+// slots without a moving obstacle are parked at -100 with the same radius.  One thread per (problem, stage, slot).
+__global__ void predict_kernel(int B, int n_dyn, int K, int p_obst, double radius, const double* __restrict__ state,
+                               double* __restrict__ params) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)B * M::N * K) return;
+  const int j = int(i % K);
+  const long bk = i / K;
+  const int k = int(bk % M::N);
+  const long b = bk / M::N;
+  double* o = params + bk * M::NPAR + p_obst + 4 * j;
+  const double t = M::DT * k;
+  if (j < n_dyn) {
+    const double* st = state + ((size_t)b * n_dyn + j) * 9;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) o[c] = st[c] + st[3 + c] * M::DT * k + 0.5 * (t * t) * st[6 + c];   // same operation order as mpcPlanner.py:158
+  } else {
+    o[0] = o[1] = o[2] = -100.0;
+  }
+  o[3] = radius;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -201,20 +296,19 @@ void rmpc_default_options(rmpc_options* o) {
   o->creep_trigger = int(c.creep_trigger); o->stall_window = int(c.stall_window);
 }
 
-constexpr int kCounterSlots = 64;
-
-static int free_all(rmpc_solver* s) {
-  cudaFree(s->counter); cudaFree(s->z_tmp);
-  cudaFree(s->d_idx); cudaFree(s->h_xinit); cudaFree(s->h_x0); cudaFree(s->h_params); cudaFree(s->h_z);
-  cudaFree(s->h_action); cudaFree(s->h_res); cudaFree(s->h_flag);
-  if (s->hstream) cudaStreamDestroy(s->hstream);
-  for (int i = 0; i < kSideStreams; ++i) {
-    if (s->side[i]) cudaStreamDestroy(s->side[i]);
-    if (s->ev_fork[i]) cudaEventDestroy(s->ev_fork[i]);
-    if (s->ev_join[i]) cudaEventDestroy(s->ev_join[i]);
+static void free_all(rmpc_solver* s) {
+  for (int i = 0; i < kSlots; ++i) {
+    Slot& sl = s->slot[i];
+    cudaFree(sl.q); cudaFree(sl.list);
+    if (sl.side) cudaStreamDestroy(sl.side);
+    if (sl.ev_fork) cudaEventDestroy(sl.ev_fork);
+    if (sl.ev_join) cudaEventDestroy(sl.ev_join);
+    if (sl.ev_done) cudaEventDestroy(sl.ev_done);
   }
-  cudaFreeHost(s->p_z); cudaFreeHost(s->p_action); cudaFreeHost(s->p_res); cudaFreeHost(s->p_flag);
-  return 0;
+  if (s->lg.exec) cudaGraphExecDestroy(s->lg.exec);
+  cudaFree(s->d_in); cudaFree(s->d_out); cudaFree(s->lat_q);
+  cudaFreeHost(s->p_in); cudaFreeHost(s->p_out);
+  if (s->hstream) cudaStreamDestroy(s->hstream);
 }
 
 rmpc_solver* rmpc_create(int device, int max_batch) {
@@ -226,10 +320,17 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
              e == cudaSuccess ? "out of range" : cudaGetErrorString(e));
     return nullptr;
   }
+  DeviceGuard guard(device);
+  if (guard.err != cudaSuccess) { snprintf(g_err, sizeof g_err, "cudaSetDevice: %s", cudaGetErrorString(guard.err)); return nullptr; }
   rmpc_solver* s = new rmpc_solver();
-  memset(s, 0, sizeof *s);
   s->device = device;
   s->max_batch = max_batch;
+  s->next_slot = 0; s->staged = false; s->pend_B = 0;
+  s->d_in = s->d_out = s->p_in = s->p_out = nullptr; s->hstream = nullptr; s->lat_q = nullptr;
+  s->u_z = s->u_action = nullptr;
+  memset(&s->u_info, 0, sizeof s->u_info);
+  memset(&s->lg, 0, sizeof s->lg);
+  memset(s->slot, 0, sizeof s->slot);
   rmpc_default_options(&s->opt);
   auto fail = [&](const char* what, cudaError_t err) -> rmpc_solver* {
     snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(err));
@@ -237,29 +338,36 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
     delete s;
     return nullptr;
   };
-  if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
-  if ((e = cudaMalloc(&s->counter, sizeof(int) * kCounterSlots)) != cudaSuccess) return fail("cudaMalloc", e);
+  for (int i = 0; i < kSlots; ++i) {
+    Slot& sl = s->slot[i];
+    if ((e = cudaMalloc(&sl.q, sizeof(int) * 4)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc(&sl.list, sizeof(int) * 2 * (size_t)max_batch)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaStreamCreateWithFlags(&sl.side, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&sl.ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&sl.ev_join, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming)) != cudaSuccess)
+      return fail("cudaEventCreate", e);
+  }
   size_t smem = kSharedPerWarp * kWarps;
   if (const char* pad = getenv("RMPC_PAD_SMEM_KB")) smem += (size_t)atoi(pad) * 1024;  // experiment knob: fewer resident problems per SM
   s->smem_bytes = smem;
-  using I = Ipm<M, double, 32>;
-  if ((e = cudaFuncSetAttribute(solve_kernel<I::kFeasible>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(solve_kernel<I::kShifted>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+  if ((e = cudaFuncSetAttribute(solve_kernel<I32::kFeasible>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(solve_kernel<I32::kShifted>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(solve_kernel<I32::kAll>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
     return fail("cudaFuncSetAttribute(shared memory)", e);
-  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel<I::kFeasible>, 32 * kWarps, smem)) != cudaSuccess ||
-      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_sh, solve_kernel<I::kShifted>, 32 * kWarps, smem)) != cudaSuccess)
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel<I32::kFeasible>, 32 * kWarps, smem)) != cudaSuccess ||
+      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_sh, solve_kernel<I32::kShifted>, 32 * kWarps, smem)) != cudaSuccess ||
+      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_all, solve_kernel<I32::kAll>, 32 * kWarps, smem)) != cudaSuccess)
     return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor", e);
-  for (int i = 0; i < kSideStreams; ++i) {
-    if ((e = cudaStreamCreateWithFlags(&s->side[i], cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
-    if ((e = cudaEventCreateWithFlags(&s->ev_fork[i], cudaEventDisableTiming)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming)) != cudaSuccess)
-      return fail("cudaEventCreate", e);
-  }
   if (const char* cap = getenv("RMPC_MAX_BLOCKS_PER_SM")) {  // experiment knob: fewer problems in flight per SM
     const int c = atoi(cap);
     if (c > 0 && c < s->blocks_per_sm) s->blocks_per_sm = c;
   }
-  if (s->blocks_per_sm < 1 || s->blocks_per_sm_sh < 1) { snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem); free_all(s); delete s; return nullptr; }
+  if (s->blocks_per_sm < 1 || s->blocks_per_sm_sh < 1 || s->blocks_per_sm_all < 1) {
+    snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem);
+    free_all(s); delete s;
+    return nullptr;
+  }
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
   s->sm_count = prop.multiProcessorCount;
@@ -269,8 +377,11 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
 
 void rmpc_destroy(rmpc_solver* s) {
   if (!s) return;
-  cudaSetDevice(s->device);
-  free_all(s);
+  {
+    DeviceGuard guard(s->device);
+    cudaDeviceSynchronize();
+    free_all(s);
+  }
   delete s;
 }
 
@@ -281,7 +392,9 @@ int rmpc_set_options(rmpc_solver* s, const rmpc_options* o) {
     snprintf(g_err, sizeof g_err, "option out of range");
     return -1;
   }
+  std::lock_guard<std::mutex> lock(s->mu);
   s->opt = *o;
+  if (s->lg.exec) { cudaGraphExecDestroy(s->lg.exec); s->lg.exec = nullptr; }   // the captured launch holds the old options
   return 0;
 }
 
@@ -291,100 +404,195 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* o) {
   return 0;
 }
 
+static SolveArgs make_args(const rmpc_solver* s, const double* xinit, const double* x0, const double* params, long p_bs, long p_ss,
+                           double* z_out, double* action_out, const rmpc_info* info) {
+  SolveArgs a;
+  a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
+  a.p_bs = p_bs; a.p_ss = p_ss;
+  memset(&a.info, 0, sizeof a.info);
+  if (info) a.info = *info;
+  a.opt = to_core(s->opt);
+  a.control_mode = s->opt.control_mode;
+  return a;
+}
+
+// the launches of one batched solve on stream `st`; the caller holds s->mu and has set the device
+static int launch_solve(rmpc_solver* s, int B, const SolveArgs& a, cudaStream_t st) {
+  Slot& sl = s->slot[s->next_slot];
+  s->next_slot = (s->next_slot + 1) % kSlots;
+  if (sl.used) CK(cudaStreamWaitEvent(st, sl.ev_done, 0));   // the call that used this slot kSlots calls ago (any stream) has finished
+  sl.used = true;
+  const long need = ((long)B + kWarps - 1) / kWarps;
+  if (B <= kSmallBatch) {   // one launch: classification inside the solve
+    CK(cudaMemsetAsync(sl.q, 0, 4 * sizeof(int), st));
+    long grid = (long)s->blocks_per_sm_all * s->sm_count;
+    if (grid > need) grid = need;
+    solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, st>>>(B, a, nullptr, nullptr, sl.q + 2);
+    g_launches++;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(sl.ev_done, st));
+    return 0;
+  }
+  CK(cudaMemsetAsync(sl.q, 0, 4 * sizeof(int), st));
+  {
+    const int warps_per_block = 8;
+    long blocks = ((long)B + warps_per_block - 1) / warps_per_block;
+    const long cap = (long)s->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    classify_kernel<<<(unsigned)blocks, 32 * warps_per_block, 0, st>>>(B, a, sl.q, sl.list, s->max_batch);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  // fork: shifted starts on the side stream, next to ...
+  CK(cudaEventRecord(sl.ev_fork, st));
+  CK(cudaStreamWaitEvent(sl.side, sl.ev_fork, 0));
+  long grid = (long)s->blocks_per_sm_sh * s->sm_count;
+  if (grid > need) grid = need;
+  solve_kernel<I32::kShifted><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, sl.side>>>(B, a, sl.list + s->max_batch, sl.q + 1, sl.q + 3);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(sl.ev_join, sl.side));
+  // ... the common case on the caller's stream.  Persistent grid: as many blocks as fit at once, never more than the problems need
+  grid = (long)s->blocks_per_sm * s->sm_count;
+  if (grid > need) grid = need;
+  solve_kernel<I32::kFeasible><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, st>>>(B, a, sl.list, sl.q, sl.q + 2);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamWaitEvent(st, sl.ev_join, 0));
+  CK(cudaEventRecord(sl.ev_done, st));
+  return 0;
+}
+
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params, double* z_out,
                      double* action_out, const rmpc_info* info, void* stream) {
   return rmpc_solve_batch_strided(s, B, xinit, x0, params, (long)M::N * M::NPAR, (long)M::NPAR, z_out, action_out, info, stream);
 }
 
-int rmpc_solve_batch_strided(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
-                             long params_batch_stride, long params_stage_stride, double* z_out, double* action_out,
-                             const rmpc_info* info, void* stream) {
+static int check_solve_args(const rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params) {
   if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
-  if (params_stage_stride != 0 && params_stage_stride < M::NPAR) { snprintf(g_err, sizeof g_err, "params_stage_stride %ld: 0 (one block for all stages) or >= npar = %d", params_stage_stride, M::NPAR); return -1; }
-  if (params_batch_stride < (params_stage_stride ? params_stage_stride * (M::N - 1) + M::NPAR : M::NPAR)) { snprintf(g_err, sizeof g_err, "params_batch_stride %ld too small", params_batch_stride); return -1; }
   if (s->opt.precision != 0) { snprintf(g_err, sizeof g_err, "precision %d is not available in this build (float64 only)", s->opt.precision); return -1; }
-  CK(cudaSetDevice(s->device));
-  cudaStream_t st = (cudaStream_t)stream;
-  int* counter = s->counter + s->counter_slot;   // two queue heads per call
-  s->counter_slot = (s->counter_slot + 2) % kCounterSlots;
-  CK(cudaMemsetAsync(counter, 0, 2 * sizeof(int), st));
-  SolveArgs a;
-  a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
-  a.p_bs = params_batch_stride; a.p_ss = params_stage_stride;
-  memset(&a.info, 0, sizeof a.info);
-  if (info) a.info = *info;
-  a.opt = to_core(s->opt);
-  a.control_mode = s->opt.control_mode;
-  using I = Ipm<M, double, 32>;
-  const long need = ((long)B + kWarps - 1) / kWarps;
-  // fork: infeasible starts on the side stream, next to ...
-  const int ss = s->side_slot;
-  s->side_slot = (ss + 1) % kSideStreams;
-  CK(cudaEventRecord(s->ev_fork[ss], st));
-  CK(cudaStreamWaitEvent(s->side[ss], s->ev_fork[ss], 0));
-  long grid = (long)s->blocks_per_sm_sh * s->sm_count;
-  if (grid > need) grid = need;
-  solve_kernel<I::kShifted><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, s->side[ss]>>>(B, a, counter + 1);
-  g_launches++;
-  CK(cudaGetLastError());
-  CK(cudaEventRecord(s->ev_join[ss], s->side[ss]));
-  // ... the common case on the caller's stream.  Persistent grid: as many blocks as fit at once, never more than the problems need
-  grid = (long)s->blocks_per_sm * s->sm_count;
-  if (grid > need) grid = need;
-  solve_kernel<I::kFeasible><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, st>>>(B, a, counter);
-  CK(cudaStreamWaitEvent(st, s->ev_join[ss], 0));
-  g_launches++;
-  CK(cudaGetLastError());
   return 0;
 }
 
+int rmpc_solve_batch_strided(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
+                             long params_batch_stride, long params_stage_stride, double* z_out, double* action_out,
+                             const rmpc_info* info, void* stream) {
+  if (check_solve_args(s, B, xinit, x0, params)) return -1;
+  if (params_stage_stride != 0 && params_stage_stride < M::NPAR) { snprintf(g_err, sizeof g_err, "params_stage_stride %ld: 0 (one block for all stages) or >= npar = %d", params_stage_stride, M::NPAR); return -1; }
+  if (params_batch_stride < (params_stage_stride ? params_stage_stride * (M::N - 1) + M::NPAR : M::NPAR)) { snprintf(g_err, sizeof g_err, "params_batch_stride %ld too small", params_batch_stride); return -1; }
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
+  const SolveArgs a = make_args(s, xinit, x0, params, params_batch_stride, params_stage_stride, z_out, action_out, info);
+  return launch_solve(s, B, a, (cudaStream_t)stream);
+}
+
+// ---- host entry points -------------------------------------------------------------------------------------------
+// Device staging: [xinit | x0 | params] and [z | action | 5 residual arrays | exitflag, iters], each section sized for
+// max_batch, plus page-locked mirrors of the outputs (and, for small batches, of the inputs).
+struct Stage {
+  size_t xinit, x0, params, in_total;          // offsets in doubles
+  size_t z, action, res, flags, out_total;
+};
+static Stage stage_layout(size_t mb) {
+  Stage L;
+  L.xinit = 0; L.x0 = mb * M::NX; L.params = L.x0 + mb * M::N * M::NVAR; L.in_total = L.params + mb * M::N * M::NPAR;
+  L.z = 0; L.action = mb * M::N * M::NVAR; L.res = L.action + mb * M::NU; L.flags = L.res + 5 * mb; L.out_total = L.flags + mb;   // 2 ints per double
+  return L;
+}
+
 static int ensure_host_staging(rmpc_solver* s) {
-  if (s->h_xinit) return 0;
-  const size_t mb = (size_t)s->max_batch;
-  CK(cudaMalloc(&s->h_xinit, sizeof(double) * mb * M::NX));
-  CK(cudaMalloc(&s->h_x0, sizeof(double) * mb * M::N * M::NVAR));
-  CK(cudaMalloc(&s->h_params, sizeof(double) * mb * M::N * M::NPAR));
-  CK(cudaMalloc(&s->h_z, sizeof(double) * mb * M::N * M::NVAR));
-  CK(cudaMalloc(&s->h_action, sizeof(double) * mb * M::NU));
-  CK(cudaMalloc(&s->h_res, sizeof(double) * mb * 5));
-  CK(cudaMalloc(&s->h_flag, sizeof(int) * mb * 2));
-  CK(cudaMallocHost(&s->p_action, sizeof(double) * mb * M::NU));
-  CK(cudaMallocHost(&s->p_res, sizeof(double) * mb * 5));
-  CK(cudaMallocHost(&s->p_flag, sizeof(int) * mb * 2));
+  if (s->staged) return 0;
+  const Stage L = stage_layout((size_t)s->max_batch);
+  cudaFree(s->d_in); cudaFree(s->d_out); cudaFreeHost(s->p_out); cudaFreeHost(s->p_in);   // leftovers of an attempt that failed half way
+  s->d_in = s->d_out = s->p_out = s->p_in = nullptr;
+  CK(cudaMalloc(&s->d_in, sizeof(double) * L.in_total));
+  CK(cudaMalloc(&s->d_out, sizeof(double) * L.out_total));
+  CK(cudaMallocHost(&s->p_out, sizeof(double) * L.out_total));
+  const Stage Ls = stage_layout((size_t)(s->max_batch < kSmallBatch ? s->max_batch : kSmallBatch));
+  CK(cudaMallocHost(&s->p_in, sizeof(double) * Ls.in_total));
+  if (!s->lat_q) CK(cudaMalloc(&s->lat_q, sizeof(int) * 4));
+  s->staged = true;
+  return 0;
+}
+
+static rmpc_info staged_info(const rmpc_solver* s, double* out, size_t mb) {
+  const Stage L = stage_layout(mb);
+  rmpc_info d;
+  d.exitflag = reinterpret_cast<int*>(out + L.flags); d.iters = d.exitflag + mb;
+  d.obj = out + L.res; d.res_stat = d.obj + mb; d.res_eq = d.obj + 2 * mb; d.res_ineq = d.obj + 3 * mb; d.res_comp = d.obj + 4 * mb;
+  (void)s;
+  return d;
+}
+
+// Small batches (B <= kSmallBatch, the single-solve latency case): inputs packed into one page-locked block, then ONE
+// captured graph = H2D copy, queue reset, single-launch solve, D2H copy.  The graph is rebuilt when B, the set of wanted
+// outputs or the options change.
+static int latency_solve(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params, bool want_z,
+                         bool want_action, bool want_info) {
+  const size_t b = (size_t)B;
+  const Stage L = stage_layout(b);   // packed for this B: one contiguous copy each way
+  memcpy(s->p_in + L.xinit, xinit, sizeof(double) * b * M::NX);
+  memcpy(s->p_in + L.x0, x0, sizeof(double) * b * M::N * M::NVAR);
+  memcpy(s->p_in + L.params, params, sizeof(double) * b * M::N * M::NPAR);
+  const int flags = (want_z ? 1 : 0) | (want_action ? 2 : 0) | (want_info ? 4 : 0);
+  if (!s->lg.exec || s->lg.B != B || s->lg.flags != flags) {
+    if (s->lg.exec) { cudaGraphExecDestroy(s->lg.exec); s->lg.exec = nullptr; }
+    const rmpc_info dinf = staged_info(s, s->d_out, b);
+    const SolveArgs a = make_args(s, s->d_in + L.xinit, s->d_in + L.x0, s->d_in + L.params, (long)M::N * M::NPAR, (long)M::NPAR,
+                                  want_z ? s->d_out + L.z : nullptr, want_action ? s->d_out + L.action : nullptr, want_info ? &dinf : nullptr);
+    cudaGraph_t graph;
+    CK(cudaStreamBeginCapture(s->hstream, cudaStreamCaptureModeThreadLocal));
+    cudaError_t e = cudaMemcpyAsync(s->d_in, s->p_in, sizeof(double) * L.in_total, cudaMemcpyHostToDevice, s->hstream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(s->lat_q, 0, 4 * sizeof(int), s->hstream);
+    if (e == cudaSuccess) {
+      long grid = (long)s->blocks_per_sm_all * s->sm_count;
+      if (grid > B) grid = B;
+      solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, s->hstream>>>(B, a, nullptr, nullptr, s->lat_q + 2);
+      e = cudaGetLastError();
+    }
+    // outputs: from the first wanted section to the end of the flags (z is large and first, so it is skipped when unwanted)
+    const size_t from = want_z ? L.z : L.action;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(s->p_out + from, s->d_out + from, sizeof(double) * (L.out_total - from), cudaMemcpyDeviceToHost, s->hstream);
+    cudaError_t e2 = cudaStreamEndCapture(s->hstream, &graph);
+    if (e != cudaSuccess || e2 != cudaSuccess) {
+      snprintf(g_err, sizeof g_err, "graph capture: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+      return -1;
+    }
+    e = cudaGraphInstantiate(&s->lg.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { s->lg.exec = nullptr; snprintf(g_err, sizeof g_err, "cudaGraphInstantiate: %s", cudaGetErrorString(e)); return -1; }
+    s->lg.B = B; s->lg.flags = flags;
+  }
+  CK(cudaGraphLaunch(s->lg.exec, s->hstream));
+  g_launches++;
   return 0;
 }
 
 int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,
                                 double* z_out, double* action_out, const rmpc_info* info) {
-  if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
-  if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
+  if (check_solve_args(s, B, xinit, x0, params)) return -1;
+  std::lock_guard<std::mutex> lock(s->mu);
   if (s->pend_B) { snprintf(g_err, sizeof g_err, "a host solve is already in flight on this handle: call rmpc_wait first"); return -1; }
-  CK(cudaSetDevice(s->device));
+  GUARD(s);
   if (ensure_host_staging(s)) return -1;
   const size_t b = (size_t)B, mb = (size_t)s->max_batch;
-  cudaStream_t st = s->hstream;
-  CK(cudaMemcpyAsync(s->h_xinit, xinit, sizeof(double) * b * M::NX, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(s->h_x0, x0, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(s->h_params, params, sizeof(double) * b * M::N * M::NPAR, cudaMemcpyHostToDevice, st));
-  rmpc_info dinf;
-  memset(&dinf, 0, sizeof dinf);
-  if (info) {
-    dinf.exitflag = s->h_flag; dinf.iters = s->h_flag + mb;
-    dinf.obj = s->h_res; dinf.res_stat = s->h_res + mb; dinf.res_eq = s->h_res + 2 * mb;
-    dinf.res_ineq = s->h_res + 3 * mb; dinf.res_comp = s->h_res + 4 * mb;
-  }
-  if (rmpc_solve_batch(s, B, s->h_xinit, s->h_x0, s->h_params, z_out ? s->h_z : nullptr,
-                       action_out ? s->h_action : nullptr, info ? &dinf : nullptr, st))
-    return -1;
-  if (z_out) {
-    if (!s->p_z) CK(cudaMallocHost(&s->p_z, sizeof(double) * mb * M::N * M::NVAR));
-    CK(cudaMemcpyAsync(s->p_z, s->h_z, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyDeviceToHost, st));
-  }
-  if (action_out) CK(cudaMemcpyAsync(s->p_action, s->h_action, sizeof(double) * b * M::NU, cudaMemcpyDeviceToHost, st));
-  if (info) {
-    CK(cudaMemcpyAsync(s->p_flag, s->h_flag, sizeof(int) * (mb + b), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(s->p_res, s->h_res, sizeof(double) * (4 * mb + b), cudaMemcpyDeviceToHost, st));
+  if (B <= kSmallBatch) {
+    if (latency_solve(s, B, xinit, x0, params, z_out != nullptr, action_out != nullptr, info != nullptr)) return -1;
+  } else {
+    const Stage L = stage_layout(mb);
+    cudaStream_t st = s->hstream;
+    CK(cudaMemcpyAsync(s->d_in + L.xinit, xinit, sizeof(double) * b * M::NX, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(s->d_in + L.x0, x0, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(s->d_in + L.params, params, sizeof(double) * b * M::N * M::NPAR, cudaMemcpyHostToDevice, st));
+    const rmpc_info dinf = staged_info(s, s->d_out, mb);
+    if (info) CK(cudaMemsetAsync(dinf.exitflag, 0xff, sizeof(int) * b, st));   // -1 = "never written" would show an internal error
+    const SolveArgs a = make_args(s, s->d_in + L.xinit, s->d_in + L.x0, s->d_in + L.params, (long)M::N * M::NPAR, (long)M::NPAR,
+                                  z_out ? s->d_out + L.z : nullptr, action_out ? s->d_out + L.action : nullptr, info ? &dinf : nullptr);
+    if (launch_solve(s, B, a, st)) return -1;
+    if (z_out) CK(cudaMemcpyAsync(s->p_out + L.z, s->d_out + L.z, sizeof(double) * b * M::N * M::NVAR, cudaMemcpyDeviceToHost, st));
+    if (action_out) CK(cudaMemcpyAsync(s->p_out + L.action, s->d_out + L.action, sizeof(double) * b * M::NU, cudaMemcpyDeviceToHost, st));
+    if (info) CK(cudaMemcpyAsync(s->p_out + L.res, s->d_out + L.res, sizeof(double) * (L.out_total - L.res), cudaMemcpyDeviceToHost, st));
   }
   s->pend_B = B; s->u_z = z_out; s->u_action = action_out;
   memset(&s->u_info, 0, sizeof s->u_info);
@@ -394,19 +602,24 @@ int rmpc_solve_batch_host_async(rmpc_solver* s, int B, const double* xinit, cons
 
 int rmpc_wait(rmpc_solver* s) {
   if (!s) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
-  CK(cudaSetDevice(s->device));
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
   CK(cudaStreamSynchronize(s->hstream));
   if (!s->pend_B) return 0;
-  const size_t b = (size_t)s->pend_B, mb = (size_t)s->max_batch;
+  const size_t b = (size_t)s->pend_B;
+  const size_t lb = s->pend_B <= kSmallBatch ? b : (size_t)s->max_batch;   // small batches are packed for their own B
   s->pend_B = 0;
-  if (s->u_z) memcpy(s->u_z, s->p_z, sizeof(double) * b * M::N * M::NVAR);
-  if (s->u_action) memcpy(s->u_action, s->p_action, sizeof(double) * b * M::NU);
+  const Stage L = stage_layout(lb);
+  if (s->u_z) memcpy(s->u_z, s->p_out + L.z, sizeof(double) * b * M::N * M::NVAR);
+  if (s->u_action) memcpy(s->u_action, s->p_out + L.action, sizeof(double) * b * M::NU);
   const rmpc_info& u = s->u_info;
-  if (u.exitflag) memcpy(u.exitflag, s->p_flag, sizeof(int) * b);
-  if (u.iters) memcpy(u.iters, s->p_flag + mb, sizeof(int) * b);
+  const rmpc_info h = staged_info(s, s->p_out, lb);
+  if (u.exitflag) memcpy(u.exitflag, h.exitflag, sizeof(int) * b);
+  if (u.iters) memcpy(u.iters, h.iters, sizeof(int) * b);
   double* dst[5] = {u.obj, u.res_stat, u.res_eq, u.res_ineq, u.res_comp};
+  const double* src[5] = {h.obj, h.res_stat, h.res_eq, h.res_ineq, h.res_comp};
   for (int i = 0; i < 5; ++i)
-    if (dst[i]) memcpy(dst[i], s->p_res + i * mb, sizeof(double) * b);
+    if (dst[i]) memcpy(dst[i], src[i], sizeof(double) * b);
   return 0;
 }
 
@@ -418,17 +631,10 @@ int rmpc_solve_batch_host(rmpc_solver* s, int B, const double* xinit, const doub
 
 int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void* stream) {
   if (!s || !z || !x0 || B <= 0) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
-  CK(cudaSetDevice(s->device));
-  cudaStream_t st = (cudaStream_t)stream;
-  const long total = (long)B * M::N * M::NVAR;
-  const double* src = z;
-  if (z == x0) {  // in-place: stage the plan in the (free) z workspace first
-    if (B > s->max_batch) { snprintf(g_err, sizeof g_err, "B exceeds max_batch for in-place shift"); return -1; }
-    if (!s->z_tmp) CK(cudaMalloc(&s->z_tmp, sizeof(double) * (size_t)s->max_batch * M::N * M::NVAR));
-    CK(cudaMemcpyAsync(s->z_tmp, z, sizeof(double) * total, cudaMemcpyDeviceToDevice, st));
-    src = s->z_tmp;
-  }
-  shift_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(total, src, x0);
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
+  const long total = (long)B * M::NVAR;
+  shift_kernel<<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream>>>(total, z, x0);
   g_launches++;
   CK(cudaGetLastError());
   return 0;
@@ -439,16 +645,29 @@ int rmpc_set_params(rmpc_solver* s, int B, double* params, const int* idx, int n
   if (!s || !params || !idx || !values || B <= 0 || n_idx <= 0) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
   for (int j = 0; j < n_idx; ++j)
     if (idx[j] < 0 || idx[j] >= M::NPAR) { snprintf(g_err, sizeof g_err, "parameter index %d out of range", idx[j]); return -1; }
-  CK(cudaSetDevice(s->device));
-  cudaStream_t st = (cudaStream_t)stream;
-  if (n_idx > s->d_idx_cap) {
-    if (s->d_idx) CK(cudaFree(s->d_idx));
-    CK(cudaMalloc(&s->d_idx, sizeof(int) * n_idx));
-    s->d_idx_cap = n_idx;
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
+  for (int off = 0; off < n_idx; off += kMaxIdx) {   // the indices travel by value with the launch: nothing shared between calls
+    IdxList il;
+    il.n = n_idx - off < kMaxIdx ? n_idx - off : kMaxIdx;
+    for (int j = 0; j < il.n; ++j) il.v[j] = idx[off + j];
+    const long total = (long)B * M::N * il.n;
+    scatter_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, n_idx, off, stage_varying, il, values, params);
+    g_launches++;
+    CK(cudaGetLastError());
   }
-  CK(cudaMemcpyAsync(s->d_idx, idx, sizeof(int) * n_idx, cudaMemcpyHostToDevice, st));
-  const long total = (long)B * M::N * n_idx;
-  scatter_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(B, n_idx, stage_varying, s->d_idx, values, params);
+  return 0;
+}
+
+int rmpc_predict_obstacles(rmpc_solver* s, int B, const double* obst_state, int n_dyn, int n_slots, int p_obst, double radius,
+                           double* params, void* stream) {
+  if (!s || !params || B <= 0 || n_dyn < 0 || n_slots <= 0 || (n_dyn > 0 && !obst_state)) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  if (p_obst < 0 || p_obst + 4 * n_slots > M::NPAR) { snprintf(g_err, sizeof g_err, "obstacle slots %d..%d outside the parameter vector (npar = %d)", p_obst, p_obst + 4 * n_slots, M::NPAR); return -1; }
+  if (n_dyn > n_slots) n_dyn = n_slots;   // the reference ignores obstacles beyond number_obstacles (mpcPlanner.py:146-147)
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
+  const long total = (long)B * M::N * n_slots;
+  predict_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, n_dyn, n_slots, p_obst, radius, obst_state, params);
   g_launches++;
   CK(cudaGetLastError());
   return 0;
@@ -473,7 +692,8 @@ int rmpc_fsd_constraints(rmpc_solver* s, int B, const double* points, int n_poin
       a.idx[c] = idx[c];
     }
   }
-  CK(cudaSetDevice(s->device));
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
   const long warps = (long)B * M::N;
   fsd_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, (cudaStream_t)stream>>>(a);
   g_launches++;
