@@ -114,6 +114,10 @@ int rmpc_wait(rmpc_solver* s);
  * the horizon of one variable, no scratch copy). */
 int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void* stream);
 
+/* Initial guess for `initialization: current_state` (mpcPlanner.py:228-232 setX0): x0[b][k][0:nx] = xinit[b] for every
+ * stage k; the input part of x0 is left as it is.  Device pointers. */
+int rmpc_set_x0(rmpc_solver* s, int B, const double* xinit, double* x0, void* stream);
+
 /* Batched parameter scatter (the set* loops of mpcPlanner.py:120-210): for every problem b and every stage k,
  * params[b][k][idx[j]] = values[b][j] (stage_varying == 0, values is [B][n_idx]) or values[b][k][j]
  * (stage_varying == 1, values is [B][N][n_idx]).  idx is a HOST array of paramMap indices (it travels by value with

@@ -138,48 +138,49 @@ RMPC_HD void load_params(const ParamView<T>& pv, int k, T* p) {
 // ------------------------------------------------------------------------------------------------
 // Shared (per problem) storage.  GPU: shared memory of the warp that owns the problem; host: heap.
 template <class M> struct Dims {
-  static constexpr int NDS = (M::BASE == 0) ? M::NQ : M::NVAR;   // variables coupled by the dense part of the stage Hessian
-  static constexpr int NQD = NDS * (NDS + 1) / 2;
-  static constexpr int NHD = M::NVAR - NDS > 0 ? M::NVAR - NDS : 1;  // variables with a diagonal-only Hessian
-  static constexpr int NVA = M::NVAR + 3;                         // [A B]-sized blocks carry 3 extra columns: g0, g1, adjoint
-  static constexpr int NKK = M::NU * M::NX + 2 * M::NU;           // feedback gain K and the two feed-forward vectors
-  static constexpr int NPRE = NQD + NHD + 2 * M::NVAR;            // Hessian + g1 + gl: dead once phase 1 of the sweep has read them
-  static constexpr int OFF0 = NPRE > NKK ? NPRE : NKK;            // offset of g0 (live until the line search) in StageShared::Qs
-  static constexpr int OFF1 = OFF0 - 2 * M::NVAR, OFFL = OFF0 - M::NVAR;
-  static constexpr int LDF = (NVA % 2) ? NVA : NVA + 1;           // odd row stride of F / PAB: row- and column-wise accesses are conflict-free
-  // dense Hessian part: packed lower triangle stored column by column, so that the lane that owns column b reads
-  // entry (a, b), a >= b, at qcol(b) + a with a compile-time `a`
-  static constexpr RMPC_HD int qcol(int b) { return b * (NDS - 1) - b * (b - 1) / 2; }
-  static constexpr RMPC_HD int qidx(int a, int b) { return a >= b ? qcol(b) + a : qcol(a) + b; }
+  // The Riccati algebra runs on the variables the Newton system couples (DynS::NXC states + NU inputs, "compact" indices)
+  static constexpr int RX = DynS<M>::NXC, RV = RX + M::NU;
+  static constexpr int NDS = (M::BASE == 0) ? M::NQ : RV;          // variables coupled by the dense part of the stage Hessian
+  static constexpr int NQD = NDS * NDS;                            // stored in full, column by column: a lane reads its column with compile-time offsets
+  static constexpr int NHD = RV - NDS > 0 ? RV - NDS : 1;          // variables with a diagonal-only Hessian
+  static constexpr int NVA = RV + 3;                               // [A B]-sized blocks carry 3 extra columns: g0, g1, adjoint
+  static constexpr int NKK = M::NU * RX + 2 * M::NU;               // feedback gain K and the two feed-forward vectors
+  static constexpr int NPRE = NQD + NHD + 2 * RV;                  // Hessian + g1 + gl: dead once phase 1 of the sweep has read them
+  static constexpr int OFF0 = NPRE > NKK ? NPRE : NKK;             // offset of g0 (live until the line search) in StageShared::Qs
+  static constexpr int OFF1 = OFF0 - 2 * RV, OFFL = OFF0 - RV;
+  static constexpr int LDF = (NVA % 2) ? NVA : NVA + 1;            // odd row stride of F / PAB: row- and column-wise accesses are conflict-free
+  static constexpr int NQS0 = OFF0 + RV > 2 * M::NH ? OFF0 + RV : 2 * M::NH;
+  static constexpr int NQS = NQS0 + (NQS0 & 1);                    // even: what follows stays 16-byte aligned
 };
 
 template <class M, class T>
-struct StageShared {
+struct alignas(16) StageShared {
   T z[M::NVAR];
   T dz[M::NVAR];             // Newton step of this stage (written by the roll-out)
-  // [Qd | Hd | .. | g1 | gl | g0]: dense Hessian part (Dims::qidx), diagonal entries of the variables NDS..NVAR-1,
-  // g1 = -G'(1/s) (coefficient of mu in the barrier gradient), gl = cost gradient - G' lambda, g0 = cost gradient.
+  // [Qd | Hd | .. | g1 | gl | g0] over the compact variables: dense Hessian part (NDS x NDS, symmetric, both triangles),
+  // diagonal entries of the variables NDS..RV-1, g1 = -G'(1/s) (coefficient of mu in the barrier gradient),
+  // gl = cost gradient - G' lambda, g0 = cost gradient.
   // Everything before g0 is dead once phase 1 of the sweep has consumed it; K | kff0 | kff1 then reuse that space.
   // After the roll-out the same array is scratch for the line search: row values of the trial point in [0, NH), multiplier
   // steps in [NH, 2 NH).
-  T Qs[Dims<M>::OFF0 + M::NVAR > 2 * M::NH ? Dims<M>::OFF0 + M::NVAR : 2 * M::NH];
+  T Qs[Dims<M>::NQS];
   T ABv[DynS<M>::NABV];      // z-dependent entries of [A B]
   T d[M::NX];                // Phi(z_k) - x_{k+1}
   T nu01[2];                 // adjoint of (X+, Y+) from the previous sweep (diff-drive curvature)
-  RMPC_HD T g0(int i) const { return Qs[Dims<M>::OFF0 + i]; }
-  RMPC_HD T& K(int l, int c) { return Qs[l * M::NX + c]; }
-  RMPC_HD T K(int l, int c) const { return Qs[l * M::NX + c]; }
-  RMPC_HD T& kff0(int l) { return Qs[M::NU * M::NX + l]; }
-  RMPC_HD T kff0(int l) const { return Qs[M::NU * M::NX + l]; }
-  RMPC_HD T& kff1(int l) { return Qs[M::NU * M::NX + M::NU + l]; }
-  RMPC_HD T kff1(int l) const { return Qs[M::NU * M::NX + M::NU + l]; }
+  RMPC_HD T g0(int c) const { return Qs[Dims<M>::OFF0 + c]; }
+  RMPC_HD T& K(int l, int c) { return Qs[l * Dims<M>::RX + c]; }
+  RMPC_HD T K(int l, int c) const { return Qs[l * Dims<M>::RX + c]; }
+  RMPC_HD T& kff0(int l) { return Qs[M::NU * Dims<M>::RX + l]; }
+  RMPC_HD T kff0(int l) const { return Qs[M::NU * Dims<M>::RX + l]; }
+  RMPC_HD T& kff1(int l) { return Qs[M::NU * Dims<M>::RX + M::NU + l]; }
+  RMPC_HD T kff1(int l) const { return Qs[M::NU * Dims<M>::RX + M::NU + l]; }
 };
 
 template <class M, class T>
 struct ProblemShared {
   StageShared<M, T> st[M::N];
-  T PAB[M::NX * Dims<M>::LDF];     // P_{k+1} [A B | d-term | p1 | nu] of the stage being processed
-  T F[M::NVAR * Dims<M>::LDF];     // [Q | g0 | g1 | gl] + [A B]' PAB: lower triangle of the matrix part, Fxx mirrored
+  T PAB[Dims<M>::RX * Dims<M>::LDF];   // P_{k+1} [A B | d-term | p1 | nu] of the stage being processed (compact variables)
+  T F[Dims<M>::RV * Dims<M>::LDF];     // [Q | g0 | g1 | gl] + [A B]' PAB, every entry valid (the matrix part is symmetric up to rounding)
 };
 
 template <class T>
@@ -194,8 +195,9 @@ struct Ipm {
   static constexpr int NX = M::NX, NU = M::NU, NV = M::NVAR, NH = M::NH, N = M::N, NQ = M::NQ;
   static constexpr int NGEO1 = M::NGEO > 0 ? M::NGEO : 1;
   static constexpr int SLOTS = (N + G - 1) / G;
-  static constexpr int NVA = Dims<M>::NVA, NDS = Dims<M>::NDS;
+  static constexpr int NVA = Dims<M>::NVA, NDS = Dims<M>::NDS, RX = Dims<M>::RX, RV = Dims<M>::RV;
   using DS = DynS<M>;
+  static_assert(DS::rows_avoid_inert(), "a limit row touches a state that the Newton system leaves out");
 
   const Group<G>& g;
   ProblemShared<M, T>& S;
@@ -275,7 +277,10 @@ struct Ipm {
         }
         constexpr int NQD = Dims<M>::NQD;
         RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) { st.Qs[Dims<M>::OFF0 + i] = sd.g[i]; st.Qs[Dims<M>::OFF1 + i] = q1[i]; st.Qs[Dims<M>::OFFL + i] = glv[i]; }
+        for (int c = 0; c < RV; ++c) {
+          const int i = DS::full(c);
+          st.Qs[Dims<M>::OFF0 + c] = sd.g[i]; st.Qs[Dims<M>::OFF1 + c] = q1[i]; st.Qs[Dims<M>::OFFL + c] = glv[i];
+        }
         if constexpr (SH) {
           // A shifted row is treated like a violated equality h + shift(1 - alpha) >= 0: the Newton step is asked to
           // remove the whole shift, ds = g'dz - shift, which adds (lambda/s) shift g to the mu-free right-hand side.
@@ -291,20 +296,22 @@ struct Ipm {
           RMPC_UNROLL
           for (int r = 0; r < M::NLIM; ++r) q0[M::lim_var(r)] -= T(M::lim_sign(r)) * sig[M::lim_row(r)] * T(sh[sl][M::lim_row(r)]);
           RMPC_UNROLL
-          for (int i = 0; i < NV; ++i) st.Qs[Dims<M>::OFF0 + i] = q0[i];
+          for (int c = 0; c < RV; ++c) st.Qs[Dims<M>::OFF0 + c] = q0[DS::full(c)];
         }
-        // dense part of the Hessian (lower triangle, Dims::qidx) with the diagonal folded in
+        // dense part of the Hessian (NDS x NDS, both triangles, column by column) with the diagonal folded in; q comes
+        // first in both variable orders, so the q-block keeps its indices
         T Qd[NQD];
         RMPC_UNROLL
         for (int i = 0; i < NQD; ++i) Qd[i] = T(0);
         RMPC_UNROLL
         for (int a = 0; a < NQ; ++a)
           RMPC_UNROLL
-          for (int b = 0; b <= a; ++b) Qd[Dims<M>::qidx(a, b)] = sd.Hqq[a * NQ + b];
+          for (int b = 0; b < NQ; ++b) Qd[b * NDS + a] = sd.Hqq[a * NQ + b];
         RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) {
-          if (i < NDS) Qd[Dims<M>::qidx(i, i)] += sd.Hd[i] + reg;
-          else st.Qs[NQD + (i < NDS ? 0 : i - NDS)] = sd.Hd[i] + reg;
+        for (int c = 0; c < RV; ++c) {
+          const int i = DS::full(c);
+          if (c < NDS) Qd[(c < NDS ? c : 0) * NDS + (c < NDS ? c : 0)] += sd.Hd[i] + reg;
+          else st.Qs[NQD + (c < NDS ? 0 : c - NDS)] = sd.Hd[i] + reg;
         }
         if (k < N - 1) {
           T xn[NX], ABv[DS::NABV], Hc[5][5];
@@ -322,8 +329,11 @@ struct Ipm {
             RMPC_UNROLL
             for (int a = 0; a < 5; ++a)
               RMPC_UNROLL
-              for (int b = 0; b < 5; ++b)
-                if (DS::vc(a) >= DS::vc(b)) Qd[Dims<M>::qidx(DS::vc(a), DS::vc(b))] += Hc[a][b];
+              for (int b = 0; b < 5; ++b) {
+                constexpr int dummy = 0;
+                const int ca = DS::comp(DS::vc(a)) < 0 ? dummy : DS::comp(DS::vc(a)), cb = DS::comp(DS::vc(b)) < 0 ? dummy : DS::comp(DS::vc(b));
+                Qd[(cb < NDS ? cb : 0) * NDS + (ca < NDS ? ca : 0)] += Hc[a][b];
+              }
           }
         }
         RMPC_UNROLL
@@ -339,55 +349,53 @@ struct Ipm {
   }
 
   // ---- B: backward Riccati sweep, shared by the lanes -------------------------------------------
-  // Three barriers per stage.  P_{k+1} itself is never stored: the lanes that own its rows keep them in registers
-  // just long enough to form PAB for the next (earlier) stage.
+  // Three barriers per stage, over the RX coupled states and NU inputs (compact indices, DynS::full/comp).  P_{k+1}
+  // itself is never stored: the lanes that own its rows keep them in registers just long enough to form PAB for the next
+  // (earlier) stage.
   RMPC_HD void sweep(Red<T>& o) {
     constexpr int LDF = Dims<M>::LDF, NQD = Dims<M>::NQD;
     T res_stat = T(0), nsum = T(0);
     bool ok = true;
-    int fxx[NX];  // warp: where the lane that owns row i of P finds F(i, j) in the lower triangle (stage-invariant)
-    RMPC_UNROLL
-    for (int j = 0; j < NX; ++j) { const int i = g.lane < NX ? g.lane : 0; fxx[j] = i >= j ? i * LDF + j : j * LDF + i; }
     for (int k = N - 1; k >= 0; --k) {
       StageShared<M, T>& st = S.st[k];
       const bool dyn = k < N - 1;
-      // phase 1: lane j owns column j of F = [Q | g0 | g1 | gl] + [A B]' PAB; of the matrix part only the lower
-      // triangle (i >= j) is meaningful
+      // phase 1: lane j owns column j of F = [Q | g0 | g1 | gl] + [A B]' PAB, every row of it
       for (int j = g.lane; j < NVA; j += G) {
-        const bool rhs = j >= NV;
-        // column j of [Q | g0 | g1 | gl] starts at Qs[qoff]; the loads are unconditional (what they fetch above the
-        // diagonal is never stored)
-        const int qoff = rhs ? (j == NV ? Dims<M>::OFF0 : Dims<M>::OFF0 + (j - NV - 3) * NV) : (j < NDS ? Dims<M>::qcol(j) : 0);
-        T a[NV];
+        const bool rhs = j >= RV;
+        // column j of [Q | g0 | g1 | gl] starts at Qs[qoff]; the loads are unconditional, a column of a variable with a
+        // diagonal-only Hessian selects zeros instead of what it fetched
+        const int qoff = rhs ? (j == RV ? Dims<M>::OFF0 : Dims<M>::OFF0 + (j - RV - 3) * RV) : (j < NDS ? j * NDS : 0);
+        const bool take = rhs || j < NDS;
+        T a[RV];
         RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) {
+        for (int i = 0; i < RV; ++i) {
           const T q = st.Qs[qoff + i];
-          if (i < NDS) a[i] = q;
+          if (i < NDS) a[i] = (NDS == RV || take) ? q : T(0);
           else { const T h = st.Qs[NQD + (i < NDS ? 0 : i - NDS)]; a[i] = rhs ? q : (j == i ? h : T(0)); }
         }
         if (dyn) {
           T abv[DS::NABV];
           RMPC_UNROLL
           for (int i = 0; i < DS::NVR * DS::NVC; ++i) abv[i] = st.ABv[i];
-          T w[NX];
+          T w[RX];
           RMPC_UNROLL
-          for (int l = 0; l < NX; ++l) w[l] = S.PAB[l * LDF + j];
+          for (int l = 0; l < RX; ++l) w[l] = S.PAB[l * LDF + j];
           RMPC_UNROLL
-          for (int i = 0; i < NV; ++i)
+          for (int i = 0; i < RV; ++i)
             RMPC_UNROLL
-            for (int e = 0; e < DS::n(i); ++e) a[i] += DS::template val<T>(i, e, abv) * w[DS::row(i, e)];
+            for (int e = 0; e < DS::cn(i); ++e) a[i] += DS::template cv<T>(i, e, abv) * w[DS::crow(i, e)];
         }
         RMPC_UNROLL
-        for (int i = 0; i < NV; ++i) S.F[i * LDF + j] = a[i];  // above the diagonal: junk that nobody reads
+        for (int i = 0; i < RV; ++i) S.F[i * LDF + j] = a[i];
       }
       g.sync();
-      // phase 2: Cholesky of Fuu (every lane, redundantly) and the NX+2 solves (one column per lane)
+      // phase 2: Cholesky of Fuu (every lane, redundantly) and the RX+2 solves (one column per lane)
       {
         T L[NU * NU];
         RMPC_UNROLL
         for (int a = 0; a < NU; ++a)
           RMPC_UNROLL
-          for (int b = 0; b <= a; ++b) L[a * NU + b] = S.F[(NX + a) * LDF + NX + b];
+          for (int b = 0; b <= a; ++b) L[a * NU + b] = S.F[(RX + a) * LDF + RX + b];
         RMPC_UNROLL
         for (int j = 0; j < NU; ++j) {
           T dd = L[j * NU + j];
@@ -405,13 +413,13 @@ struct Ipm {
           }
         }
         RMPC_UNROLL
-        for (int j = 0; j < NU; ++j) res_stat = tmax(res_stat, tabs(S.F[(NX + j) * LDF + NV + 2]));
-        for (int c = g.lane; c < NX + 2; c += G) {
-          const int col = c < NX ? c : NV + (c - NX);
+        for (int j = 0; j < NU; ++j) res_stat = tmax(res_stat, tabs(S.F[(RX + j) * LDF + RV + 2]));
+        for (int c = g.lane; c < RX + 2; c += G) {
+          const int col = c < RX ? c : RV + (c - RX);
           T y[NU];
           RMPC_UNROLL
           for (int i = 0; i < NU; ++i) {
-            T v = S.F[(NX + i) * LDF + col];
+            T v = S.F[(RX + i) * LDF + col];
             RMPC_UNROLL
             for (int l = 0; l < i; ++l) v -= L[i * NU + l] * y[l];
             y[i] = v * L[i * NU + i];
@@ -425,27 +433,27 @@ struct Ipm {
           }
           RMPC_UNROLL
           for (int i = 0; i < NU; ++i) {
-            st.Qs[c < NX ? i * NX + c : NU * NX + (c - NX) * NU + i] = -y[i];  // K(i, c) | kff0(i) | kff1(i)
+            st.Qs[c < RX ? i * RX + c : NU * RX + (c - RX) * NU + i] = -y[i];  // K(i, c) | kff0(i) | kff1(i)
           }
         }
       }
       g.sync();
       // phase 3: lane i owns row i of P = Fxx + Fux' K, p = fx + Fux' kff and the adjoint nu (x-part of the Lagrangian
       // gradient), and turns them at once into row i of PAB = P [A B | d-term | p1 | nu] of the stage before
-      for (int i = g.lane; i < NX; i += G) {
+      for (int i = g.lane; i < RX; i += G) {
         T fu[NU];
         RMPC_UNROLL
-        for (int l = 0; l < NU; ++l) fu[l] = S.F[(NX + l) * LDF + i];
-        T Pi[NX];
+        for (int l = 0; l < NU; ++l) fu[l] = S.F[(RX + l) * LDF + i];
+        T Pi[RX];
         RMPC_UNROLL
-        for (int j = 0; j < NX; ++j) {
-          T v = (G > 1) ? S.F[fxx[j]] : S.F[i >= j ? i * LDF + j : j * LDF + i];  // Fxx from its lower triangle
+        for (int j = 0; j < RX; ++j) {
+          T v = S.F[i * LDF + j];
           RMPC_UNROLL
           for (int l = 0; l < NU; ++l) v += fu[l] * st.K(l, j);
           Pi[j] = v;
         }
-        T p0 = S.F[i * LDF + NV], p1 = S.F[i * LDF + NV + 1];
-        const T nui = S.F[i * LDF + NV + 2];
+        T p0 = S.F[i * LDF + RV], p1 = S.F[i * LDF + RV + 1];
+        const T nui = S.F[i * LDF + RV + 2];
         RMPC_UNROLL
         for (int l = 0; l < NU; ++l) { p0 += fu[l] * st.kff0(l); p1 += fu[l] * st.kff1(l); }
         nsum += tabs(nui);
@@ -456,18 +464,18 @@ struct Ipm {
           RMPC_UNROLL
           for (int j = 0; j < DS::NVR * DS::NVC; ++j) abv[j] = sp.ABv[j];
           RMPC_UNROLL
-          for (int j = 0; j < NV; ++j) {
+          for (int j = 0; j < RV; ++j) {
             T a = T(0);
             RMPC_UNROLL
-            for (int e = 0; e < DS::n(j); ++e) a += DS::template val<T>(j, e, abv) * Pi[DS::row(j, e)];
+            for (int e = 0; e < DS::cn(j); ++e) a += DS::template cv<T>(j, e, abv) * Pi[DS::crow(j, e)];
             S.PAB[i * LDF + j] = a;
           }
           T a = p0;
           RMPC_UNROLL
-          for (int l = 0; l < NX; ++l) a += Pi[l] * sp.d[l];
-          S.PAB[i * LDF + NV] = a;
-          S.PAB[i * LDF + NV + 1] = p1;
-          S.PAB[i * LDF + NV + 2] = nui;
+          for (int l = 0; l < RX; ++l) a += Pi[l] * sp.d[DS::full(l)];
+          S.PAB[i * LDF + RV] = a;
+          S.PAB[i * LDF + RV + 1] = p1;
+          S.PAB[i * LDF + RV + 2] = nui;
         }
       }
       g.sync();
@@ -479,11 +487,15 @@ struct Ipm {
   }
 
   // ---- C: forward roll-out: dz_k = (dx_k, K_k dx_k + kff_k), dx_{k+1} = [A B] dz_k + d_k, into shared memory.
-  // Lane j < NU evaluates row j of the feedback law, the rows are exchanged by shuffles, and every lane carries dx.
+  // Lane j < NU evaluates row j of the feedback law, the rows are exchanged by shuffles, and every lane carries dx (the
+  // coupled states) and di (the states the Newton system leaves out: di+ = di + d).
   RMPC_HD void rollout(const T mu) {
-    T dx[NX];
+    constexpr int NI = NX - RX > 0 ? NX - RX : 1;
+    T dx[RX], di[NI];
     RMPC_UNROLL
-    for (int i = 0; i < NX; ++i) dx[i] = T(0);  // x_1 is fixed
+    for (int i = 0; i < RX; ++i) dx[i] = T(0);  // x_1 is fixed
+    RMPC_UNROLL
+    for (int i = 0; i < NI; ++i) di[i] = T(0);
     for (int k = 0; k < N; ++k) {
       StageShared<M, T>& st = S.st[k];
       T u[NU];
@@ -492,33 +504,39 @@ struct Ipm {
         for (int j = 0; j < NU; ++j) {
           T a = st.kff0(j) + mu * st.kff1(j);
           RMPC_UNROLL
-          for (int i = 0; i < NX; ++i) a += st.K(j, i) * dx[i];
+          for (int i = 0; i < RX; ++i) a += st.K(j, i) * dx[i];
           u[j] = a;
         }
       } else {
         const int j = g.lane < NU ? g.lane : 0;
         T a = st.kff0(j) + mu * st.kff1(j), b = T(0);
         RMPC_UNROLL
-        for (int i = 0; i + 1 < NX; i += 2) { a += st.K(j, i) * dx[i]; b += st.K(j, i + 1) * dx[i + 1]; }
-        if (NX % 2) a += st.K(j, NX - 1) * dx[NX - 1];
+        for (int i = 0; i + 1 < RX; i += 2) { a += st.K(j, i) * dx[i]; b += st.K(j, i + 1) * dx[i + 1]; }
+        if (RX % 2) a += st.K(j, RX - 1) * dx[RX - 1];
         a += b;
         RMPC_UNROLL
         for (int l = 0; l < NU; ++l) u[l] = g.bcast(a, l);
       }
       RMPC_UNROLL
-      for (int i = 0; i < NX; ++i) st.dz[i] = dx[i];      // same value from every lane
+      for (int i = 0; i < RX; ++i) st.dz[DS::full(i)] = dx[i];      // same value from every lane
       RMPC_UNROLL
       for (int j = 0; j < NU; ++j) st.dz[NX + j] = u[j];
+      if (NX > RX) {
+        int c = 0;
+        RMPC_UNROLL
+        for (int f = 0; f < NX; ++f)
+          if (DS::comp(f) < 0) { st.dz[f] = di[c < NI ? c : 0]; if (k < N - 1) di[c < NI ? c : 0] += st.d[f]; ++c; }
+      }
       if (k < N - 1) {
-        T dn[NX];
+        T dn[RX];
         RMPC_UNROLL
-        for (int i = 0; i < NX; ++i) dn[i] = st.d[i];
+        for (int i = 0; i < RX; ++i) dn[i] = st.d[DS::full(i)];
         RMPC_UNROLL
-        for (int j = 0; j < NV; ++j)
+        for (int j = 0; j < RV; ++j)
           RMPC_UNROLL
-          for (int e = 0; e < DS::n(j); ++e) dn[DS::row(j, e)] += DS::template val<T>(j, e, st.ABv) * (j < NX ? dx[j < NX ? j : 0] : u[j < NX ? 0 : j - NX]);
+          for (int e = 0; e < DS::cn(j); ++e) dn[DS::crow(j, e)] += DS::template cv<T>(j, e, st.ABv) * (j < RX ? dx[j < RX ? j : 0] : u[j < RX ? 0 : j - RX]);
         RMPC_UNROLL
-        for (int i = 0; i < NX; ++i) dx[i] = dn[i];
+        for (int i = 0; i < RX; ++i) dx[i] = dn[i];
       }
     }
     g.sync();
@@ -708,7 +726,7 @@ struct Ipm {
           T gd[NH];
           row_dirs(sl, k, gd);
           RMPC_UNROLL
-          for (int i = 0; i < NV; ++i) dphi += S.st[k].g0(i) * S.st[k].dz[i];
+          for (int c = 0; c < RV; ++c) dphi += S.st[k].g0(c) * S.st[k].dz[DS::full(c)];
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
             const T sr = s[sl][r], lr = lam[sl][r];

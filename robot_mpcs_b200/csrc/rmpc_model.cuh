@@ -1,6 +1,6 @@
 // rmpc_model.cuh — per-stage model functions of the robotmpcs NLP as fused device functions with analytic
 // Jacobians and (Gauss-Newton or exact) Hessians.  Everything is templated on a generated `M` traits struct
-// (robot_mpcs_b200/models/codegen.py) so the compiler sees every dimension, every kinematic constant and
+// (emitted by robot_mpcs_b200/models/mpcModel.py:traits_source) so the compiler sees every dimension, every kinematic constant and
 // every parameter index as an immediate.
 //
 // What is restated here (reference paths relative to /root/reference):
@@ -620,6 +620,24 @@ struct DynS {
   }
   template <class T>
   static RMPC_HD T val(int j, int e, const T* ABv) { return var(j, e) < 0 ? T(cval(j, e)) : ABv[var(j, e) < 0 ? 0 : var(j, e)]; }
+
+  // Variables the Newton system couples ("compact" indices).  The diff-drive state carries three entries (x3..x5, the
+  // world-frame velocities of the planar pose, diff_drive_mpc_model.py:24-31) that are constant under the dynamics,
+  // enter no cost and no row, and feed no other state: their Newton step is dx+ = dx + d, their multipliers are zero, and
+  // the Riccati algebra runs without them (5 states instead of 8).  Holonomic models: every variable is coupled.
+  static constexpr int NXC = (M::BASE == 0) ? M::NX : 5;
+  static constexpr int NVCP = NXC + M::NU;
+  static constexpr RMPC_HD int full(int c) { return M::BASE == 0 ? c : (c < 3 ? c : c + 3); }
+  static constexpr RMPC_HD int comp(int f) { return M::BASE == 0 ? f : (f < 3 ? f : (f < 6 ? -1 : f - 3)); }
+  static constexpr RMPC_HD int cn(int jc) { return n(full(jc)); }
+  static constexpr RMPC_HD int crow(int jc, int e) { return comp(row(full(jc), e)); }
+  template <class T>
+  static RMPC_HD T cv(int jc, int e, const T* ABv) { return val<T>(full(jc), e, ABv); }
+  static constexpr RMPC_HD bool rows_avoid_inert() {
+    for (int r = 0; r < M::NLIM; ++r)
+      if (comp(M::lim_var(r)) < 0) return false;
+    return true;
+  }
 };
 
 // x+ = Phi(z) and the z-dependent Jacobian entries ABv (see DynS).  If `exact`, Hc (5x5 over VC, diff-drive only)

@@ -229,6 +229,15 @@ __global__ void shift_kernel(long total, const double* __restrict__ z, double* _
   dst[(M::N - 1) * M::NVAR] = nxt;
 }
 
+// "current_state" initial guess (planner/mpcPlanner.py:228-232): the state part of every stage <- xinit, inputs untouched
+__global__ void guess_kernel(long total, const double* __restrict__ xinit, double* __restrict__ x0) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int v = int(i % M::NX);
+  const long bk = i / M::NX;
+  x0[bk * M::NVAR + v] = xinit[(bk / M::N) * M::NX + v];
+}
+
 struct IdxList { int n; int v[kMaxIdx]; };
 
 __global__ void scatter_kernel(int B, int n_all, int off, int stage_varying, const __grid_constant__ IdxList idx,
@@ -255,11 +264,12 @@ __global__ void predict_kernel(int B, int n_dyn, int K, int p_obst, double radiu
   const int k = int(bk % M::N);
   const long b = bk / M::N;
   double* o = params + bk * M::NPAR + p_obst + 4 * j;
-  const double t = M::DT * k;
+  const double t = __dmul_rn(M::DT, double(k));
   if (j < n_dyn) {
     const double* st = state + ((size_t)b * n_dyn + j) * 9;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) o[c] = st[c] + st[3 + c] * M::DT * k + 0.5 * (t * t) * st[6 + c];   // same operation order as mpcPlanner.py:158
+    for (int c = 0; c < 3; ++c)   // the operation order of mpcPlanner.py:158, without fused multiply-adds: the same bits as the Python line
+      o[c] = __dadd_rn(__dadd_rn(st[c], __dmul_rn(__dmul_rn(st[3 + c], M::DT), double(k))), __dmul_rn(__dmul_rn(0.5, __dmul_rn(t, t)), st[6 + c]));
   } else {
     o[0] = o[1] = o[2] = -100.0;
   }
@@ -635,6 +645,17 @@ int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void*
   GUARD(s);
   const long total = (long)B * M::NVAR;
   shift_kernel<<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream>>>(total, z, x0);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int rmpc_set_x0(rmpc_solver* s, int B, const double* xinit, double* x0, void* stream) {
+  if (!s || !xinit || !x0 || B <= 0) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
+  const long total = (long)B * M::N * M::NX;
+  guess_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(total, xinit, x0);
   g_launches++;
   CK(cudaGetLastError());
   return 0;

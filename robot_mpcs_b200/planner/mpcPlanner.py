@@ -113,9 +113,14 @@ class MPCPlanner(object):
         return t
 
     def _set(self, name, values, stage_varying=False):
-        """params[:, :, paramMap[name]] = values ([B|1, len] or [B|1, N, len])."""
+        """params[:, :, paramMap[name]] = values ([B|1, len] or [B|1, N, len]).  Device resident: one launch of the
+        library's scatter kernel (rmpc_set_params) — the set* loops of mpcPlanner.py:120-210 for the whole batch."""
         idx = self._paramMap[name]
         v = self._as(values, 2 if stage_varying else 1)
+        if self._device_resident:
+            shape = (self._B, self._config.time_horizon, len(idx)) if stage_varying else (self._B, len(idx))
+            self._solver.set_params(self._params3, idx, v.expand(*shape))
+            return
         if not stage_varying:
             v = v[:, None, :]
         self._params3[:, :, idx] = v
@@ -176,22 +181,27 @@ class MPCPlanner(object):
             self._set("lin_constrs_" + str(i), lc[:, :, i, :], stage_varying=True)
 
     def updateDynamicObstacles(self, obstArray):
-        """obstArray[(B,) 3*m*n_dyn] = per obstacle (pos, vel, acc); constant-acceleration prediction per stage
-        (intent of mpcPlanner.py:144-161)."""
+        """obstArray[(B,) 3*m*n_dyn] = per obstacle (pos, vel, acc); stage i sees pos + vel (i dt) + acc (i dt)^2 / 2 with
+        radius self._r, obstacle slots beyond the moving ones are parked at -100 (mpcPlanner.py:144-161; the reference
+        reads the first obstacle's block for every j and calls a missing self.dt() — its evident intent is followed).
+        Device resident: rmpc_predict_obstacles, one kernel for the whole batch."""
         a = self._as(obstArray, 1)
         m, K, N = self.m(), self._config.number_obstacles, self._config.time_horizon
-        nb = a.shape[1] // (3 * m)
-        t = (np.arange(N) * self.dt())
+        nb = min(K, a.shape[1] // (3 * m))
+        p_obst = self._paramMap["obst"][0]
         if self._device_resident:
-            t = torch.as_tensor(t, dtype=torch.float64, device=a.device)
+            st = a[:, : nb * 3 * m].reshape(a.shape[0], nb, 3 * m).expand(self._B, nb, 3 * m) if nb else None
+            self._solver.predict_obstacles(self._params3, st, K, p_obst, self._r)
+            return
+        i = np.arange(N, dtype=np.float64)[None, :, None]
         for j in range(K):
             idx = self._paramMap["obst"][j * (m + 1): (j + 1) * (m + 1)]
             if j < nb:
                 blk = a[:, j * 3 * m: (j + 1) * 3 * m]
-                pos, vel, acc = blk[:, :m], blk[:, m:2 * m], blk[:, 2 * m:3 * m]
-                pred = pos[:, None, :] + vel[:, None, :] * t[None, :, None] + 0.5 * acc[:, None, :] * (t ** 2)[None, :, None]
+                pos, vel, acc = blk[:, None, :m], blk[:, None, m:2 * m], blk[:, None, 2 * m:3 * m]
+                pred = pos + vel * self.dt() * i + 0.5 * (self.dt() * i) ** 2 * acc       # mpcPlanner.py:158, same operation order
             else:
-                pred = self._zeros(1, N, m) - 100.0
+                pred = np.zeros((1, N, m)) - 100.0
             self._params3[:, :, idx[:m]] = pred
             self._params3[:, :, idx[m]] = self._r
 
@@ -239,7 +249,10 @@ class MPCPlanner(object):
 
     def setX0(self, initialize_type="current_state", initial_step=True):
         if initialize_type == "current_state" or (initialize_type == "previous_plan" and initial_step):
-            self._x0[:, :, : self._nx] = self._xinit[:, None, :]
+            if self._device_resident:
+                self._solver.set_x0(self._xinit, self._x0)
+            else:
+                self._x0[:, :, : self._nx] = self._xinit[:, None, :]
             self._initial_step = False
         elif initialize_type == "previous_plan":
             self.shiftHorizon(self._z_prev)

@@ -41,7 +41,7 @@ class RmpcInfo(ctypes.Structure):
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
            "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_strided", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
-           "rmpc_set_params", "rmpc_launch_count"]
+           "rmpc_set_params", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_launch_count"]
 
 
 class SolverError(RuntimeError):
@@ -75,6 +75,9 @@ def load_library(solver_dir: str) -> ctypes.CDLL:
     lib.rmpc_fsd_constraints.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_long,
                                          ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_int,
                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_void_p]
+    lib.rmpc_set_x0.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.rmpc_predict_obstacles.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                           ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
     lib.rmpc_launch_count.restype = ctypes.c_long
     return lib
 
@@ -165,7 +168,7 @@ class Solver:
         out = {"action": act, "z": z}
         info = RmpcInfo()
         if want_info:
-            out["exitflag"] = torch.empty(B, dtype=torch.int32, device=dev)
+            out["exitflag"] = torch.full((B,), -1, dtype=torch.int32, device=dev)   # -1 = never written (an internal error, include/rmpc.h)
             out["iters"] = torch.empty(B, dtype=torch.int32, device=dev)
             for k in ("obj", "res_stat", "res_eq", "res_ineq", "res_comp"):
                 out[k] = torch.empty(B, dtype=f64, device=dev)
@@ -233,6 +236,16 @@ class Solver:
             raise SolverError(self._err())
         return x0
 
+    def set_x0(self, xinit, x0):
+        """x0[B,N,nvar] (CUDA): state part of every stage <- xinit[B,nx] (mpcPlanner.py:228-232)."""
+        B = x0.shape[0]
+        self._ensure(B)
+        xinit = xinit.to(torch.float64).contiguous()
+        stream = torch.cuda.current_stream(x0.device).cuda_stream
+        if self.lib.rmpc_set_x0(self._h, B, xinit.data_ptr(), x0.data_ptr(), ctypes.c_void_p(stream)) != 0:
+            raise SolverError(self._err())
+        return x0
+
     def set_params(self, params, idx, values):
         """params[B,N,npar] (CUDA, float64) <- values[B,len(idx)] or values[B,N,len(idx)] at paramMap indices idx."""
         B = params.shape[0]
@@ -243,6 +256,19 @@ class Solver:
         stream = torch.cuda.current_stream(params.device).cuda_stream
         if self.lib.rmpc_set_params(self._h, B, params.data_ptr(), idx_arr, len(idx), values.data_ptr(), sv,
                                     ctypes.c_void_p(stream)) != 0:
+            raise SolverError(self._err())
+        return params
+
+    def predict_obstacles(self, params, obst_state, n_slots, p_obst, radius):
+        """params[B,N,npar] (CUDA) <- constant-acceleration prediction of the moving obstacles obst_state[B,n_dyn,9]
+        (mpcPlanner.py:144-161) in the `obst` slots starting at parameter index p_obst."""
+        B = params.shape[0]
+        self._ensure(B)
+        n_dyn = 0 if obst_state is None else obst_state.shape[1]
+        st = obst_state.to(torch.float64).contiguous() if n_dyn else None
+        stream = torch.cuda.current_stream(params.device).cuda_stream
+        if self.lib.rmpc_predict_obstacles(self._h, B, st.data_ptr() if n_dyn else None, n_dyn, n_slots, p_obst, float(radius),
+                                           params.data_ptr(), ctypes.c_void_p(stream)) != 0:
             raise SolverError(self._err())
         return params
 

@@ -232,6 +232,22 @@ def panda(pmap, B, N=20, npar=50, seed=1, jitter=True):
         q0 = np.clip(q0, PANDA_LIMITS[:, 0] + 0.05, PANDA_LIMITS[:, 1] - 0.05)
         goal = goal + g.uniform(-0.15, 0.15, (B, 3))
         oc = oc + g.uniform(-0.1, 0.1, (B, 3))
+    if jitter:
+        # "reject if any h < 0.02 at start" — a measured state that already touches the obstacle makes
+        # the NLP infeasible (x_1 = xinit is fixed and the rows apply at stage 1).  Scenarios whose draw is fine keep it;
+        # the others get a new obstacle centre from a second, equally seeded stream.
+        import os
+        from robot_mpcs_b200.utils.urdf import KinematicTree
+        links = ["panda_link3", "panda_link5", "panda_link7"]
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets", "panda.urdf")) as f:
+            pos = KinematicTree(f.read()).positions(q0, "panda_link0", "panda_link7", links)
+        g2 = _rng(seed + 1000)
+        for _ in range(50):
+            clear = np.min([np.linalg.norm(pos[l] - oc, axis=1) for l in links], axis=0) - 0.1 - 0.14
+            bad = clear < 0.02
+            if not bad.any():
+                break
+            oc[bad] = np.array([0.5, -0.3, 0.3]) + g2.uniform(-0.1, 0.1, (int(bad.sum()), 3))
     P = np.zeros((B, N, npar))
     _fill(P, pmap, "r_body", [0.14])
     _fill(P, pmap, "obst", np.concatenate([oc, 0.1 * np.ones((B, 1))], 1))

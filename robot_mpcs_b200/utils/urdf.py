@@ -72,3 +72,30 @@ class KinematicTree:
 
     def n_movable(self, root: str, end: str) -> int:
         return sum(1 for j in self.chain(root, end) if j.kind != 0)
+
+    def positions(self, q, root: str, end: str, links):
+        """Numeric forward kinematics (numpy, batched): q[B, n] over the movable joints of the root->end chain, in chain
+        order -> {link: position[B, 3] in the root frame}.  The same chain product the generated device code evaluates
+        (csrc/rmpc_model.cuh kin_frames); used by the scenario generators to reject states that start in collision."""
+        import numpy as np
+        q = np.asarray(q, dtype=np.float64)
+        qi = {j.name: i for i, j in enumerate(jt for jt in self.chain(root, end) if jt.kind != 0)}
+        out = {}
+        for link in links:
+            R = np.broadcast_to(np.eye(3), (q.shape[0], 3, 3)).copy()
+            t = np.zeros((q.shape[0], 3))
+            for jt in self.chain(root, link):
+                t = t + R @ np.array(jt.t)
+                R = R @ np.array(jt.R).reshape(3, 3)
+                if jt.kind == 0:
+                    continue
+                a = np.array(jt.axis)
+                v = q[:, qi[jt.name]]
+                if jt.kind == 2:
+                    t = t + (R @ a) * v[:, None]
+                else:
+                    K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+                    Rj = np.eye(3)[None] + np.sin(v)[:, None, None] * K[None] + (1 - np.cos(v))[:, None, None] * (K @ K)[None]
+                    R = R @ Rj
+            out[link] = t
+        return out

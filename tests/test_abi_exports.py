@@ -12,7 +12,7 @@ from conftest import ROOT, SOLVERS
 def _declared():
     hdr = open(os.path.join(ROOT, "include", "rmpc.h")).read()
     hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
-    return sorted(set(re.findall(r"\b(rmpc_[a-z_]+)\s*\(", hdr)))
+    return sorted(set(re.findall(r"\b(rmpc_[a-z0-9_]+)\s*\(", hdr)))
 
 
 def test_header_declares_the_abi():
