@@ -3,10 +3,13 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--batch B] [--impl ours|reference]
 
-A "step" is one batched solve of `batch` synthetic scenarios per GPU (weak scaling).  Default workload at
-N=1 is BASELINE.json configs[1]: boxer diff-drive, N=30, 5 sphere obstacles, batch 4096.
-Prints ONE JSON line (rank 0).  `--impl reference` times the CPU path (oracle/cpu_twin.cpp, all host threads)
-on the same workload; the reference's own solver (FORCESPRO-generated C) is proprietary and absent.
+A "step" is one batched solve of `batch` synthetic scenarios per GPU (weak scaling).  The headline workload at N=1 is
+BASELINE.json configs[1]: boxer diff-drive, N=30, 5 sphere obstacles, batch 4096.  The same
+line carries, under "workloads", one sub-record for every other BASELINE config (pointRobot_example, panda B=1024,
+supermarket B=16384, the pointRobot sweep incl. B = 10^3..10^6), each measured in this run with its own roofline, CPU
+baseline, end-to-end leg and single-solve latency.  Prints ONE JSON line (rank 0).  `--impl reference` times the CPU path
+(oracle/cpu_twin.cpp, all host threads) on the same workload; the reference's own solver (FORCESPRO-generated C) is
+proprietary and absent.
 """
 from __future__ import annotations
 
@@ -28,25 +31,19 @@ from robot_mpcs_b200 import scenarios as sc  # noqa: E402
 
 SOLVERS = os.path.join(ROOT, "robot_mpcs_b200", "solvers")
 
-# name -> (solver dir, generator, default batch, F_iter flop/iteration (SURVEY §8d convention), description)
+# name -> (solver dir, generator, default batch, F_iter flop/iteration (SURVEY §8d convention), stage-invariant parameters?, description)
 WORKLOADS = {
-    "boxer_radial": ("boxer_n3_01_H30_noSlack", sc.boxer_radial, 4096, 94e3,
+    "boxer_radial": ("boxer_n3_01_H30_noSlack", sc.boxer_radial, 4096, 94e3, True,
                      "boxer diff-drive N=30, 5 sphere obstacles (BASELINE configs[1])"),
-    "pointRobot_sweep": ("pointRobot_n3_005_H20_noSlack", sc.point_robot_sweep, 131072, 34e3,
+    "pointRobot_sweep": ("pointRobot_n3_005_H20_noSlack", sc.point_robot_sweep, 131072, 34e3, True,
                          "pointRobot N=20, goal + 1 sphere obstacle, random scenarios (BASELINE configs[4])"),
-    "panda": ("panda_n7_005_H20_noSlack", sc.panda, 1024, 351e3,
+    "panda": ("panda_n7_005_H20_noSlack", sc.panda, 1024, 351e3, True,
               "panda 7-DoF N=20, FK-sphere self-collision + joint limits (BASELINE configs[2])"),
-    "boxer_supermarket": ("boxer_n3_01_H40_noSlack", sc.boxer_supermarket, 16384, 127e3,
+    "boxer_supermarket": ("boxer_n3_01_H40_noSlack", sc.boxer_supermarket, 16384, 127e3, False,
                           "boxer N=40, 8 stage-varying half-planes (BASELINE configs[3])"),
 }
-
-
-# dram__bytes_read.sum + dram__bytes_write.sum of one solve at the default batch (ncu --set full, each kernel captured
-# alone with a cold L2), and where it is kept.  A solve is two concurrent launches: solve_kernel<1> (feasible starts,
-# 13.3 ms alone) and solve_kernel<2> (infeasible starts: for this workload it reads every problem once, finds none and
-# exits after 38 us).  Both read the inputs, hence twice the algorithmic bytes when neither finds them in L2.
-NCU_TRAFFIC = {"boxer_radial": ((52.855296e6 + 0.603392e6) + (52.525568e6 + 0.399104e6), "profiles/r1m_ncu_boxer_radial_B4096.txt")}
-
+SUB_WORKLOADS = ["pointRobot_sweep", "panda", "boxer_supermarket"]   # measured next to the headline, time-boxed
+SWEEP_B = [1000, 10000, 100000, 1000000]                             # BASELINE configs[4]: 10^3 .. 10^6 scenarios (whole job)
 
 _OUT = None
 
@@ -63,8 +60,34 @@ def load_paramMap(sdir):
 
 
 def make_inputs(workload, B, seed):
-    sdir, gen, _, _, _ = WORKLOADS[workload]
+    sdir, gen = WORKLOADS[workload][:2]
     return gen(load_paramMap(sdir), B, seed=seed)
+
+
+def make_inputs_device(torch, dev, workload, B, seed, N):
+    """Scenario batch on the device in the reference layout.  Workloads whose parameters do not vary over the horizon are
+    generated for one stage and tiled on the device (the generators repeat one block N times anyway)."""
+    sdir, gen, _, _, invariant, _ = WORKLOADS[workload]
+    pm = load_paramMap(sdir)
+    if not invariant:
+        s = gen(pm, B, seed=seed)
+        return {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in s.items()}
+    out = {"xinit": [], "x0": [], "params": []}
+    for lo in range(0, B, 131072):
+        n = min(131072, B - lo)
+        s = gen(pm, n, N=1, seed=seed + 7919 * (lo // 131072))
+        out["xinit"].append(torch.from_numpy(s["xinit"]).to(dev))
+        out["x0"].append(torch.from_numpy(s["x0"]).to(dev).expand(n, N, -1))
+        out["params"].append(torch.from_numpy(s["params"]).to(dev).expand(n, N, -1))
+    return {k: torch.cat(v).contiguous() for k, v in out.items()}
+
+
+def workload_config(args, workload, B, world):
+    """What both arms are measured on (the same dict in both lines)."""
+    return {"workload": f"{workload}: {WORKLOADS[workload][5]}", "batch_per_gpu": B, "global_batch": B * world, "params": args.params,
+            "hessian": "exact+GN fallback" if args.hessian else "gauss-newton", "stall_window": args.stall_window,
+            "tolerances": {"tol_stat": 1e-6, "tol_eq": 1e-8, "tol_ineq": 1e-8, "tol_comp": 1e-8}, "max_iter": 200,
+            "parallelism": f"scenario-sharded x{world}, all_gather of action/exitflag/iters per step"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -91,17 +114,13 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
+    def mark(self):
+        return len(self.rows)
+
+    def summary(self, lo=0, hi=None):
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in self.rows[lo:hi]:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
                 continue
@@ -113,6 +132,15 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+    def stop(self):
+        if self.proc is None:
+            return
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
 
 
 def measure_fma_peak(torch, dev, is_double=True):
@@ -137,29 +165,34 @@ def measure_fma_peak(torch, dev, is_double=True):
     return best
 
 
-def cpu_baseline(workload, B_sample, seed, threads=0):
+def host_threads():
+    # every host core this process may use, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def cpu_baseline(workload, B_sample, seed, threads=0, inputs=None):
     """The CPU path (oracle/cpu_twin.cpp: same algorithm, float64, OpenMP over problems) on a bounded sample."""
     from oracle.build_twin import Twin
     sdir = WORKLOADS[workload][0]
     tw = Twin(os.path.join(SOLVERS, sdir))
-    s = make_inputs(workload, B_sample, seed)
-    if threads <= 0:   # every host core this process may use, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
-        threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    s = inputs if inputs is not None else make_inputs(workload, B_sample, seed)
+    B_sample = s["xinit"].shape[0]
+    threads = threads if threads > 0 else host_threads()
     tw.solve(s["xinit"][:64], s["x0"][:64], s["params"][:64], nthreads=threads)  # warm-up
     t = time.perf_counter()
     r = tw.solve(s["xinit"], s["x0"], s["params"], nthreads=threads)
     dt = time.perf_counter() - t
     conv = int((r["exitflag"] == 1).sum())
-    cores = threads
-    return {"value": conv / dt, "unit": "converged solves/s", "cores": cores, "kind": "port",
+    return {"value": conv / dt, "unit": "converged solves/s", "cores": threads, "kind": "port",
             "sample": f"{B_sample} scenarios of workload {workload} (seed {seed}), one pass, {dt:.2f} s, converged {conv}/{B_sample}, "
                       f"mean iters {float(r['iters'].mean()):.1f}"}, dt, conv
 
 
-def single_solve_latency(workload, n, solve_one):
+def single_solve_latency(workload, n, solve_one, inputs=None):
     """p50/p99 wall time of `n` single solves (B = 1) on `n` different scenarios of the workload; solve_one(xinit, x0, params)
     takes host arrays and returns once the action is back on the host (BASELINE.json metric, second half)."""
-    s = make_inputs(workload, n, seed=4242)
+    s = inputs if inputs is not None else make_inputs(workload, n, seed=4242)
+    n = s["xinit"].shape[0]
     xs, x0s, ps = (np.ascontiguousarray(s[k]) for k in ("xinit", "x0", "params"))
     for i in range(min(n, 10)):
         solve_one(xs[i:i + 1], x0s[i:i + 1], ps[i:i + 1])
@@ -174,10 +207,19 @@ def single_solve_latency(workload, n, solve_one):
             "n": n, "converged": conv}
 
 
-def cpu_single_solve_latency(workload, n):
+def cpu_single_solve_latency(workload, n, inputs=None):
     from oracle.build_twin import Twin
     tw = Twin(os.path.join(SOLVERS, WORKLOADS[workload][0]))
-    return single_solve_latency(workload, n, lambda x, x0, p: int(tw.solve(x, x0, p, nthreads=1)["exitflag"][0]))
+    return single_solve_latency(workload, n, lambda x, x0, p: int(tw.solve(x, x0, p, nthreads=1)["exitflag"][0]), inputs)
+
+
+def ncu_traffic(workload):
+    """DRAM bytes of one solve from the committed ncu capture of this build, if there is one (never measured in this run)."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        return json.load(open(p)).get(workload)
+    except Exception:
+        return None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -185,7 +227,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    _, _, defB, _, desc = WORKLOADS[args.workload]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    defB = WORKLOADS[args.workload][2]
     B = args.batch or defB
     Bs = min(B, args.ref_sample)
     times, convs = [], []
@@ -196,224 +239,297 @@ def run_reference(args):
             times.append(dt); convs.append(conv)
     val = sum(convs) / sum(times)
     base["value"] = val
+    base["sample"] = f"{args.steps} passes of {Bs} scenarios of workload {args.workload} each (seeds 100..), {sum(times):.2f} s"
     line = {"impl": "reference", "metric": "converged MPC solves/sec", "value": val, "unit": "converged solves/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {desc}", "batch_per_step": Bs, "note": "CPU twin (port) of the same IPM/Riccati; FORCESPRO/IPOPT unavailable on this box"},
+            "config": workload_config(args, args.workload, B, world),
+            "note": f"CPU twin (port) of the same IPM/Riccati on {base['cores']} host threads, {Bs} scenarios per step; FORCESPRO/IPOPT unavailable on this box",
             "cpu_baseline": base, "e2e": {"value": val, "unit": "converged solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     if args.latency_samples > 0:
         line["single_solve_latency"] = dict(cpu_single_solve_latency(args.workload, args.latency_samples), path="CPU twin, 1 thread, B=1")
     emit(line)
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
-    from robot_mpcs_b200.planner.solver import Solver
-    from robot_mpcs_b200.parallel import gather_results, init_process_group
+class Bench:
+    """One process = one GPU.  measure() runs one workload: device-resident throughput, one batch alone, end to end through
+    the host entry points, single-solve latency, CPU baseline."""
 
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the solver has no CPU fallback (use --impl reference for the CPU path)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        init_process_group("nccl", device_id=dev)   # one NCCL channel: see robot_mpcs_b200/parallel.py
-    sdir, _, defB, f_iter, desc = WORKLOADS[args.workload]
-    B = args.batch or defB
-    solver = Solver.from_directory(os.path.join(SOLVERS, sdir), device=local_rank, max_batch=B)
-    solver.set_options(precision=args.precision, hessian=args.hessian, stall_window=args.stall_window)
-    set_bytes = 8 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar)
-    # rotating input sets whose total exceeds the 126 MB L2, so that no step finds its inputs cached
-    nsets = int(min(16, max(2, -(-160e6 // set_bytes))))
-    sets = []
-    for i in range(nsets):
-        s = make_inputs(args.workload, B, seed=1000 * rank + i)
-        host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in s.items()}
-        devt = {k: v.to(dev) for k, v in host.items()}
-        if args.params == "compressed":
-            p3 = devt["params"].view(B, solver.N, solver.npar)
-            if not bool((p3 == p3[:, :1]).all()):
-                raise SystemExit(f"--params compressed: workload {args.workload} has stage-varying parameters")
-            devt["params"] = p3[:, 0].contiguous()
-        sets.append((host, devt))
-    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # 256 MB > 126 MB L2
-    nstreams = max(1, args.streams)
-    streams = [torch.cuda.Stream(dev) for _ in range(nstreams)]
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.args = torch, dist, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: the solver has no CPU fallback (use --impl reference for the CPU path)")
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            from robot_mpcs_b200.parallel import init_process_group
+            init_process_group("nccl", device_id=self.dev)   # one NCCL channel: see robot_mpcs_b200/parallel.py
+        self.flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=self.dev)  # 256 MB > 126 MB L2
+        self.sampler = ClockSampler(self.local_rank)
+        if self.rank == 0:
+            self.sampler.start()
+        self.fp64_peak = self.fp32_peak = None
 
-    def step_device(i):
-        _, d = sets[i % nsets]
-        r = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
-        # the gather runs on NCCL's stream behind this step's solve; the step's stream is not held until every rank arrives
-        g = gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True) if world > 1 else None
-        return r, g
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
 
-    def barrier():
+    def solver(self, workload, B):
+        from robot_mpcs_b200.planner.solver import Solver
+        a = self.args
+        s = Solver.from_directory(os.path.join(SOLVERS, WORKLOADS[workload][0]), device=self.local_rank, max_batch=B)
+        s.set_options(precision=a.precision, hessian=a.hessian, stall_window=a.stall_window)
+        return s
+
+    def peaks(self):
+        if self.fp64_peak is None:
+            self.fp64_peak = measure_fma_peak(self.torch, self.dev, True)
+            self.fp32_peak = measure_fma_peak(self.torch, self.dev, False)
+        return self.fp64_peak, self.fp32_peak
+
+    def throughput(self, solver, sets, steps, warmup, nstreams, B):
+        """`steps` batched solves, step i on stream i % nstreams (consecutive batches overlap: the stragglers of one batch do
+        not idle the GPU); device time from the first launch to the last completion, max over ranks."""
+        torch, dist, dev, world = self.torch, self.dist, self.dev, self.world
+        from robot_mpcs_b200.parallel import gather_results
+        streams = [torch.cuda.Stream(dev) for _ in range(nstreams)]
+        nsets = len(sets)
+
+        def run(n):
+            main = torch.cuda.current_stream(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(main)
+            for st in streams:
+                st.wait_event(e0)
+            res, gathers = [], []
+            for i in range(n):
+                with torch.cuda.stream(streams[i % nstreams]):
+                    d = sets[i % nsets]
+                    r = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
+                    # the gather runs on NCCL's stream behind this step's solve; the step's stream is not held until every rank arrives
+                    gathers.append(gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True) if world > 1 else None)
+                    res.append(r)
+            for st in streams:
+                ev = torch.cuda.Event()
+                ev.record(st)
+                main.wait_event(ev)
+            for g in gathers:   # every step's all_gather has delivered before the clock stops
+                if g is not None:
+                    g.wait()
+            e1.record(main)
+            return e0, e1, res
+
+        run(warmup)
+        self.barrier()
+        m0 = self.sampler.mark()
+        launches0 = solver.launch_count()
+        t_wall = time.perf_counter()
+        e0, e1, results = run(steps)
+        self.barrier()
+        t_wall = time.perf_counter() - t_wall
+        m1 = self.sampler.mark()
+        launches = solver.launch_count() - launches0
+        conv = sum(int((r["exitflag"] == 1).sum()) for r in results)
+        iters = sum(int(r["iters"].sum()) for r in results)
+        total_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        cnt = torch.tensor([conv, iters, B * len(results)], dtype=torch.float64, device=dev)
         if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
+            dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        return {"total_s": float(total_ms) * 1e-3, "conv": float(cnt[0]), "iters": float(cnt[1]), "solved": float(cnt[2]), "rank_iters": float(iters),
+                "launches": int(launches), "wall_s": t_wall, "clock_marks": (m0, m1)}
 
-    def run_steps(n):
-        """n batched solves, step i on stream i % nstreams (consecutive batches overlap: the stragglers of one batch no
-        longer idle the GPU); returns device time from the first launch to the last completion, and the per-step results."""
-        main = torch.cuda.current_stream(dev)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(main)
-        for st in streams:
-            st.wait_event(e0)
-        res, gathers = [], []
-        for i in range(n):
-            with torch.cuda.stream(streams[i % nstreams]):
-                r, g = step_device(i)
-                res.append(r)
-                gathers.append(g)
-        for st in streams:
-            ev = torch.cuda.Event()
-            ev.record(st)
-            main.wait_event(ev)
-        for g in gathers:   # every step's all_gather has delivered before the clock stops
-            if g is not None:
-                g.wait()
-        e1.record(main)
-        return e0, e1, res
+    def measure(self, workload, B, steps, warmup, nstreams, e2e=True, latency_samples=0, cpu_sample=0, alone=True):
+        torch, dist, dev, world, rank, a = self.torch, self.dist, self.dev, self.world, self.rank, self.args
+        sdir, _, _, f_iter, invariant, desc = WORKLOADS[workload]
+        solver = self.solver(workload, B)
+        set_bytes = 8 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar)
+        # rotating input sets whose total exceeds the 126 MB L2, so that no step finds its inputs cached
+        nsets = int(min(32, max(1 if set_bytes > 200e6 else 2, -(-200e6 // set_bytes))))
+        hosts, sets = [], []
+        for i in range(nsets):
+            if e2e:
+                s = make_inputs(workload, B, seed=1000 * rank + i)
+                host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in s.items()}
+                hosts.append(host)
+                devt = {k: v.to(dev) for k, v in host.items()}
+            else:
+                devt = make_inputs_device(torch, dev, workload, B, 1000 * rank + i, solver.N)
+            if a.params == "compressed":
+                p3 = devt["params"].view(B, solver.N, solver.npar)
+                if not bool((p3 == p3[:, :1]).all()):
+                    raise SystemExit(f"--params compressed: workload {workload} has stage-varying parameters")
+                devt["params"] = p3[:, 0].contiguous()
+            sets.append(devt)
+        tp = self.throughput(solver, sets, steps, warmup, nstreams, B)
+        total_s = tp["total_s"]
+        rec = {"value": tp["conv"] / total_s, "unit": "converged solves/s", "batch_per_gpu": B, "global_batch": B * world, "steps": steps, "warmup": warmup,
+               "ms_per_step": 1e3 * total_s / steps, "converged_fraction": tp["conv"] / tp["solved"], "mean_iters": tp["iters"] / tp["solved"],
+               "gpu_launches": tp["launches"], "wall_s": tp["wall_s"], "streams": nstreams,
+               "l2": f"{nsets} rotating input set(s) of {set_bytes / 1e6:.0f} MB (> 126 MB L2 in total)"}
+        bytes_alg = 8.0 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar) + 8.0 * B * (solver.nu + 1) + 4.0 * B * 2
+        if rank == 0:
+            rec["clocks"] = self.sampler.summary(*tp["clock_marks"])
+            fp64_peak, fp32_peak = self.peaks()
+            peaks = {}
+            try:
+                peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            except Exception:
+                pass
+            hbm_peak = peaks.get("hbm_gbs", 6650.0)
+            launch_ms = 1e3 * total_s / steps     # average launch duration over the timed region: K launches share it (they overlap on the streams)
+            flops_launch = tp["rank_iters"] * f_iter / steps
+            ach = flops_launch / (launch_ms * 1e-3) / 1e12
+            tr = ncu_traffic(workload) if not a.batch else None
+            rec["roofline"] = {"bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": (ach / fp64_peak) if fp64_peak else None,
+                               "traffic": None, "traffic_ncu": tr,
+                               "traffic_note": "DRAM bytes are not measurable inside this run; traffic_ncu is dram__bytes_read+write of one solve from the committed "
+                                               "ncu capture of this build (profiles/ncu_traffic.json), null if there is none",
+                               "peak_source": "measured in this run (csrc/peak_fma.cu DFMA chains); MEASURED_PEAKS.json has no FP64 figure",
+                               "fp32_peak_measured": fp32_peak, "kernel_ms": launch_ms, "flops_per_launch": flops_launch,
+                               "basis": "algorithmic flops = iterations x F_iter (SURVEY 8d convention: dense Riccati count); kernel_ms = timed region / launches on this rank",
+                               "hbm": {"achieved": bytes_alg / (launch_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                       "frac": bytes_alg / (launch_ms * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes": bytes_alg}}
+        # ---- one batch alone (what a closed loop sees: the next step depends on this one): L2 flushed, events around the call
+        if alone:
+            kern_ms = []
+            d = sets[0]
+            for i in range(max(3, min(steps, 8))):
+                self.flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                rr = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
+                e1.record()
+                torch.cuda.synchronize(dev)
+                kern_ms.append(e0.elapsed_time(e1))
+            k_ms = float(np.mean(kern_ms))
+            if rank == 0:
+                alone_tf = float(rr["iters"].sum()) * f_iter / (k_ms * 1e-3) / 1e12
+                rec["roofline"]["one_batch_alone"] = {"kernel_ms": k_ms, "achieved": alone_tf, "frac": (alone_tf / self.fp64_peak) if self.fp64_peak else None,
+                                                      "solves_per_s": float((rr["exitflag"] == 1).sum()) / (k_ms * 1e-3), "max_iters": int(rr["iters"].max()),
+                                                      "note": "a single batch, L2 flushed: bounded by its slowest problem (iterations x per-iteration latency of one warp)"}
+        # ---- end to end through the host entry points (pinned host buffers -> H2D -> solve -> D2H), up to three handles in flight
+        if e2e:
+            nh = min(nstreams, 3)
+            hsolvers = [solver] + [self.solver(workload, B) for _ in range(nh - 1)]
+            hnp = [{k: v.numpy() for k, v in h.items()} for h in hosts]
 
-    # ---- device-resident throughput ("value")
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()  # nvidia-smi needs ~100 ms per sample: it watches the warm-up steps as well as the timed ones
-    run_steps(args.warmup)
-    barrier()
-    launches0 = solver.launch_count()
-    t_wall = time.perf_counter()
-    e0, e1, results = run_steps(args.steps)
-    barrier()
-    t_wall = time.perf_counter() - t_wall
-    launches = solver.launch_count() - launches0
-    conv_total = sum(int((r["exitflag"] == 1).sum()) for r in results)
-    iters_total = sum(int(r["iters"].sum()) for r in results)
-    nsolved = B * len(results)
-    total_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    conv_t = torch.tensor([conv_total, iters_total, nsolved], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(conv_t, op=dist.ReduceOp.SUM)
-    clocks = sampler.stop() if rank == 0 else None
-    total_s = float(total_ms) * 1e-3
-    value = float(conv_t[0]) / total_s
+            def e2e_run(n):
+                pend, conv = [None] * nh, 0
+                for i in range(n + nh):
+                    j = i % nh
+                    if pend[j] is not None:
+                        hsolvers[j].wait()
+                        conv += int((pend[j]["exitflag"] == 1).sum())
+                        pend[j] = None
+                    if i < n:
+                        hh = hnp[i % nsets]
+                        pend[j] = hsolvers[j].solve_batch(hh["xinit"], hh["x0"], hh["params"], want_z=False, want_info=True, block=False)
+                return conv
 
-    # ---- one batch alone (roofline of the solve kernel, and the latency of a whole batch): L2 flushed, events around the launch
-    kern_ms = []
-    _, d = sets[0]
-    for i in range(max(3, min(args.steps, 10))):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        rr = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
-        e1.record()
-        torch.cuda.synchronize(dev)
-        kern_ms.append(e0.elapsed_time(e1))
-    k_ms = float(np.mean(kern_ms))
-    flops = float(rr["iters"].sum()) * f_iter
-    bytes_alg = 8.0 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar) + 8.0 * B * (solver.nu + 1) + 4.0 * B * 2
+            e2e_run(nh + 1)  # every handle allocates its staging before the clock starts
+            self.barrier()
+            e2e_steps = max(4, steps)
+            t0 = time.perf_counter()
+            e2e_conv = e2e_run(e2e_steps)
+            self.barrier()
+            e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            e2e_c = torch.tensor([e2e_conv], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+                dist.all_reduce(e2e_c, op=dist.ReduceOp.SUM)
+            rec["e2e"] = {"value": float(e2e_c) / float(e2e_t), "unit": "converged solves/s", "h2d_bytes_per_step": set_bytes,
+                          "d2h_bytes_per_step": 8 * B * (solver.nu + 5) + 4 * B * 2, "steps": e2e_steps,
+                          "api": f"rmpc_solve_batch_host_async + rmpc_wait on {nh} handle(s), pinned host buffers"}
+            del hsolvers
+        if rank == 0 and latency_samples > 0:
+            lat_in = make_inputs(workload, latency_samples, seed=4242)
 
-    # ---- end to end through the host entry points (pinned host buffers -> H2D -> solve -> D2H), two handles in flight
-    nh = min(nstreams, 3)
-    hsolvers = [solver] + [Solver.from_directory(os.path.join(SOLVERS, sdir), device=local_rank, max_batch=B) for _ in range(nh - 1)]
-    for hs in hsolvers[1:]:
-        hs.set_options(precision=args.precision, hessian=args.hessian, stall_window=args.stall_window)
-    hnp = [{k: v.numpy() for k, v in h.items()} for h, _ in sets]
+            def one(x, x0, p):
+                return int(solver.solve_batch(x, x0, p, want_z=False, want_info=True)["exitflag"][0])
+            rec["single_solve_latency"] = dict(single_solve_latency(workload, latency_samples, one, lat_in),
+                                               path="rmpc_solve_batch_host, B=1: inputs packed into one pinned block, one captured CUDA graph (H2D, single-launch "
+                                                    "solve, D2H), wall clock until the action is back on the host")
+            if world == 1 and not a.no_cpu_baseline:
+                rec["single_solve_latency"]["cpu_1_thread"] = cpu_single_solve_latency(workload, latency_samples, lat_in)
+        if rank == 0 and world == 1 and cpu_sample > 0 and not a.no_cpu_baseline:
+            rec["cpu_baseline"], _, _ = cpu_baseline(workload, min(B, cpu_sample), seed=0)
+        del sets, hosts, solver
+        torch.cuda.empty_cache()
+        return rec
 
-    def e2e_run(n):
-        pend, conv = [None] * nh, 0
-        for i in range(n + nh):
-            j = i % nh
-            if pend[j] is not None:
-                hsolvers[j].wait()
-                conv += int((pend[j]["exitflag"] == 1).sum())
-                pend[j] = None
-            if i < n:
-                hh = hnp[i % nsets]
-                pend[j] = hsolvers[j].solve_batch(hh["xinit"], hh["x0"], hh["params"], want_z=False, want_info=True, block=False)
-        return conv
-
-    e2e_run(nh + 1)  # every handle allocates its staging before the clock starts
-    barrier()
-    e2e_steps = max(4, args.steps)   # same K as the device-resident run: a 10-step run left a fifth of its time to the last stragglers
-    t0 = time.perf_counter()
-    e2e_conv = e2e_run(e2e_steps)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    e2e_c = torch.tensor([e2e_conv], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(e2e_c, op=dist.ReduceOp.SUM)
-    h2d = set_bytes
-    d2h = 8 * B * (solver.nu + 5) + 4 * B * 2
-
-    lat = None
-    if rank == 0 and args.latency_samples > 0:
-        def one(x, x0, p):
-            return int(solver.solve_batch(x, x0, p, want_z=False, want_info=True)["exitflag"][0])
-        lat = dict(single_solve_latency(args.workload, args.latency_samples, one),
-                   path="rmpc_solve_batch_host, B=1: H2D of xinit/x0/params + one-warp solve + D2H of action/info, wall clock")
-
-    if rank == 0:
-        peaks = {}
+    def point_robot_example(self):
+        """BASELINE configs[0]: the reference's own pointRobot example, one problem (exact constants of pointRobot_example.py)."""
+        import yaml
+        from robot_mpcs_b200.planner.solver import Solver
+        sdir = "pointRobot_n3_005_H20_noSlack"
+        s = sc.point_robot_example(load_paramMap(sdir))
+        solver = Solver.from_directory(os.path.join(SOLVERS, sdir), device=self.local_rank, max_batch=1)
+        r = solver.solve_batch(s["xinit"], s["x0"], s["params"])
+        n = 1000
+        rep = {k: np.repeat(v, n, axis=0) for k, v in s.items()}
+        rec = {"exitflag": int(r["exitflag"][0]), "iters": int(r["iters"][0]), "obj": float(r["obj"][0]), "action": r["action"][0].tolist(),
+               "single_solve_latency": dict(single_solve_latency("pointRobot_sweep", n, lambda x, x0, p: int(solver.solve_batch(x, x0, p, want_z=False)["exitflag"][0]), rep),
+                                            path="rmpc_solve_batch_host, B=1, the same problem 1000 times")}
         try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            gold = json.load(open(os.path.join(ROOT, "tests", "golden", "pointRobot_example.json")))
+            rec["oracle_obj"] = gold["obj"]
+            rec["traj_rel_err_vs_oracle"] = float(np.abs(r["z"][0] - np.array(gold["Z"])).max() / np.abs(np.array(gold["Z"])).max())
         except Exception:
             pass
-        fp64_peak = measure_fma_peak(torch, dev, True)
-        fp32_peak = measure_fma_peak(torch, dev, False)
-        hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        # average launch duration over the timed region: K launches share total_s (they overlap on the streams)
-        rank_iters = float(iters_total)
-        launch_ms = 1e3 * total_s / args.steps
-        flops_launch = rank_iters * f_iter / args.steps
-        achieved_tf = flops_launch / (launch_ms * 1e-3) / 1e12
-        alone_tf = flops / (k_ms * 1e-3) / 1e12
-        base = None
-        if world == 1 and not args.no_cpu_baseline:
-            base, _, _ = cpu_baseline(args.workload, min(B, args.ref_sample), seed=0)
-        line = {
-            "metric": "converged MPC solves/sec", "value": value, "unit": "converged solves/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64" if args.precision == 0 else "f64+f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {desc}", "batch_per_gpu": B, "global_batch": B * world, "params": args.params,
-                       "l2": f"{nsets} rotating input sets of {set_bytes / 1e6:.0f} MB (> 126 MB L2 in total); single-batch timing with L2 flushed (256 MB write)",
-                       "streams": nstreams, "stall_window": args.stall_window, "hessian": "exact+GN fallback" if args.hessian else "gauss-newton",
-                       "tolerances": {k: v for k, v in solver.options().items() if k.startswith("tol")},
-                       "parallelism": f"scenario-sharded x{world}, all_gather of action/exitflag/iters per step"},
-            "converged_fraction": float(conv_t[0] / conv_t[2]), "mean_iters": float(conv_t[1] / conv_t[2]),
-            "wall_s": t_wall, "gpu_launches": int(launches),
-            "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                         "frac": (achieved_tf / fp64_peak) if fp64_peak else None,
-                         "traffic": NCU_TRAFFIC[args.workload][0] if args.workload in NCU_TRAFFIC and not args.batch else None,
-                         "traffic_source": NCU_TRAFFIC.get(args.workload, (None, None))[1],
-                         "peak_source": "measured in this run (csrc/peak_fma.cu DFMA chains); MEASURED_PEAKS.json has no FP64 figure",
-                         "fp32_peak_measured": fp32_peak, "kernel_ms": launch_ms, "flops_per_launch": flops_launch,
-                         "basis": "algorithmic flops = iterations x F_iter (SURVEY 8d convention); kernel_ms = timed region / launches on this rank (launches overlap on the streams)",
-                         "one_batch_alone": {"kernel_ms": k_ms, "achieved": alone_tf, "frac": (alone_tf / fp64_peak) if fp64_peak else None,
-                                             "solves_per_s": float((rr["exitflag"] == 1).sum()) / (k_ms * 1e-3),
-                                             "note": "a single batch, L2 flushed: bounded by its slowest problem (iterations x per-iteration latency of one warp)"},
-                         "hbm": {"achieved": bytes_alg / (launch_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                                 "frac": bytes_alg / (launch_ms * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes": bytes_alg}},
-            "e2e": {"value": float(e2e_c) / float(e2e_t), "unit": "converged solves/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "api": f"rmpc_solve_batch_host_async + rmpc_wait on {nh} handle(s), pinned host buffers"},
-            "clocks": clocks,
-        }
-        if base is not None:
-            line["cpu_baseline"] = base
-        if lat is not None:
-            line["single_solve_latency"] = lat
-            if world == 1 and not args.no_cpu_baseline:
-                line["cpu_baseline"]["single_solve_latency"] = cpu_single_solve_latency(args.workload, args.latency_samples)
+        if not self.args.no_cpu_baseline:
+            rec["single_solve_latency"]["cpu_1_thread"] = cpu_single_solve_latency("pointRobot_sweep", n, rep)
+        return rec
+
+
+def run_ours(args):
+    b = Bench(args)
+    rank, world = b.rank, b.world
+    defB = WORKLOADS[args.workload][2]
+    B = args.batch or defB
+    nstreams = max(1, args.streams)
+    rec = b.measure(args.workload, B, args.steps, args.warmup, nstreams, e2e=True, latency_samples=args.latency_samples if world == 1 else 0,
+                    cpu_sample=args.ref_sample)
+    subs = {}
+    if not args.no_workloads and args.workload == "boxer_radial" and not args.batch:
+        k = max(3, min(10, args.steps))
+        for w in SUB_WORKLOADS:   # the other BASELINE configs, time-boxed: fewer steps, a smaller CPU sample
+            subs[w] = b.measure(w, WORKLOADS[w][2], k, 3, nstreams, e2e=True, latency_samples=args.latency_samples if world == 1 else 0,
+                                cpu_sample=1024 if w == "panda" else 2048)
+        sweep = []
+        for Bt in SWEEP_B:        # BASELINE configs[4]: whole-job batch 10^3 .. 10^6, sharded over the ranks
+            per = -(-Bt // world)
+            r = b.measure("pointRobot_sweep", per, 3 if Bt >= 100000 else 10, 3, nstreams, e2e=False, latency_samples=0, cpu_sample=0, alone=False)
+            sweep.append({kk: r[kk] for kk in ("value", "batch_per_gpu", "global_batch", "ms_per_step", "converged_fraction", "mean_iters", "steps")}
+                         | ({"roofline_frac": r["roofline"]["frac"]} if "roofline" in r else {}))
+        if rank == 0:
+            subs["pointRobot_sweep"]["batch_sweep"] = sweep
+            if world == 1:
+                subs["pointRobot_example"] = b.point_robot_example()
+    if rank == 0:
+        b.sampler.stop()
+        line = {"metric": "converged MPC solves/sec", "value": rec["value"], "unit": "converged solves/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64" if args.precision == 0 else "f64+f32", "data": "synthetic",
+                "config": workload_config(args, args.workload, B, world),
+                "run": {"streams": nstreams, "l2": rec["l2"] + "; single-batch timing with L2 flushed (256 MB write)",
+                        "note": "value needs several batches in flight (streams); roofline.one_batch_alone is what a closed loop, whose next step depends on this one, gets"},
+                "converged_fraction": rec["converged_fraction"], "mean_iters": rec["mean_iters"], "wall_s": rec["wall_s"], "gpu_launches": rec["gpu_launches"],
+                "roofline": rec["roofline"], "e2e": rec["e2e"], "clocks": rec["clocks"]}
+        for k in ("cpu_baseline", "single_solve_latency"):
+            if k in rec:
+                line[k] = rec[k]
+        if subs:
+            line["workloads"] = subs
         emit(line)
     if world > 1:
-        dist.destroy_process_group()
+        b.dist.destroy_process_group()
 
 
 def main():
@@ -428,12 +544,13 @@ def main():
     ap.add_argument("--hessian", type=int, default=1)
     ap.add_argument("--ref-sample", type=int, default=4096, help="scenarios per CPU-baseline pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the sub-records of the other BASELINE configs")
     ap.add_argument("--params", default="reference", choices=["reference", "compressed"],
                     help="device-resident parameter format: the reference's all_parameters[N*npar] per problem, or one npar block per problem "
                          "for workloads whose parameters do not vary over the horizon (rmpc_solve_batch_strided, stage stride 0)")
     ap.add_argument("--streams", type=int, default=4, help="CUDA streams the consecutive batches are spread over (1 = strictly one batch at a time)")
     ap.add_argument("--stall-window", type=int, default=0, help="rmpc_options.stall_window (0 = off, the default)")
-    ap.add_argument("--latency-samples", type=int, default=300, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
+    ap.add_argument("--latency-samples", type=int, default=1000, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     # Libraries write to file descriptor 1 behind Python's back (NCCL's version banner at NCCL_DEBUG=VERSION ignores

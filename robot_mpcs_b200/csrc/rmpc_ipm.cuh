@@ -150,7 +150,14 @@ template <class M> struct Dims {
   static constexpr int OFF1 = OFF0 - 2 * RV, OFFL = OFF0 - RV;
   static constexpr int LDF = (NVA % 2) ? NVA : NVA + 1;            // odd row stride of F / PAB: row- and column-wise accesses are conflict-free
   static constexpr int NQS0 = OFF0 + RV > 2 * M::NH ? OFF0 + RV : 2 * M::NH;
-  static constexpr int NQS = NQS0 + (NQS0 & 1);                    // even: what follows stays 16-byte aligned
+  static constexpr int NQS1 = NQS0 + (NQS0 & 1);                   // even: what follows stays 16-byte aligned
+  // In the stage-parallel phases lane k works on stage k, so the lanes of a warp access shared memory with the stage
+  // stride.  The stride (in doubles) is kept = 2 (mod 4): 16-byte aligned, conflict-free for 128-bit accesses and two-way
+  // for 64-bit ones.  A multiple of 16 puts every lane on the same bank (measured: 45 % of all shared wavefronts were
+  // conflicts with a 112-double stage, 10 % with 126).
+  static constexpr int STAGE0 = 2 * M::NVAR + NQS1 + DynS<M>::NABV + M::NX + 2;
+  static constexpr int STAGE1 = STAGE0 + (STAGE0 & 1);             // what alignas(16) rounds the struct to
+  static constexpr int NQS = NQS1 + ((STAGE1 % 4 == 2) ? 0 : 2);
 };
 
 template <class M, class T>
@@ -178,6 +185,7 @@ struct alignas(16) StageShared {
 
 template <class M, class T>
 struct ProblemShared {
+  static_assert(sizeof(T) != 8 || (sizeof(StageShared<M, T>) / 8) % 4 == 2, "stage stride must be 2 (mod 4) doubles");
   StageShared<M, T> st[M::N];
   T PAB[Dims<M>::RX * Dims<M>::LDF];   // P_{k+1} [A B | d-term | p1 | nu] of the stage being processed (compact variables)
   T F[Dims<M>::RV * Dims<M>::LDF];     // [Q | g0 | g1 | gl] + [A B]' PAB, every entry valid (the matrix part is symmetric up to rounding)
@@ -611,6 +619,12 @@ struct Ipm {
     load_guess(xinit, z_in);
     T mu = T(opt.mu0);
     bool pole0 = false, shifted = false;
+    if constexpr (MODE != kFeasible) {  // lanes without a stage take part in the "any shift left?" votes: they must hold zeros, not what the last problem left
+      RMPC_UNROLL
+      for (int sl = 0; sl < SLOTS; ++sl)
+        RMPC_UNROLL
+        for (int r = 0; r < NH; ++r) sh[sl][r] = 0.0f;
+    }
     RMPC_UNROLL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
