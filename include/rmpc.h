@@ -134,6 +134,24 @@ int rmpc_set_params(rmpc_solver* s, int B, double* params, const int* idx, int n
 int rmpc_predict_obstacles(rmpc_solver* s, int B, const double* obst_state, int n_dyn, int n_slots, int p_obst, double radius,
                            double* params, void* stream);
 
+/* A batched solve that allocates nothing.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arrays, layouts and results as rmpc_solve_batch (device pointers owned by the caller, asynchronous on `stream`), but
+ * there is no handle: the scratch memory of the solve (queue heads + the two problem lists of the classification pass)
+ * is a file-scope device array of 131 328 bytes inside the library, held by every GPU that loads it until the process
+ * exits, and the call performs no cudaMalloc / cudaFree / stream or event creation.  Limits and rules:
+ *   - B <= rmpc_static_max_batch() = 16384; a larger B is refused with an error (rmpc_last_error);
+ *   - runs on the calling thread's CURRENT device; the first call on a device does a one-time set-up (symbol address,
+ *     kernel attributes, occupancy query — no allocation), so make that first call outside graph capture;
+ *   - every call shares the one array (it is cleared at the start of each call, in stream order): calls that overlap on
+ *     the GPU — two streams, or two host threads on two streams — race and give wrong results; serialise them;
+ *   - the three kernels run one after the other on `stream` (no side stream), so a batch with many infeasible starts
+ *     is slower than through a handle;
+ *   - opt may be NULL (defaults); precision must be 0. */
+int rmpc_solve_batch_static(int B, const double* xinit, const double* x0, const double* params, double* z_out,
+                            double* action_out, const rmpc_info* info, const rmpc_options* opt, void* stream);
+int rmpc_static_max_batch(void);
+
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py reports it). */
 long rmpc_launch_count(void);
 

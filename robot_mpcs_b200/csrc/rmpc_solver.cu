@@ -722,4 +722,102 @@ int rmpc_fsd_constraints(rmpc_solver* s, int B, const double* points, int n_poin
   return 0;
 }
 
+
+// ---- rmpc_solve_batch_static: a batched solve that allocates nothing --------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch memory of a solve — the two
+// queue heads and the two problem lists the classification pass fills — lives in a file-scope device array instead of
+// the handle's cudaMalloc'ed slots.  Every GPU that loads this library holds the array until the process exits.
+constexpr int kStaticMaxBatch = 16384;                       // problems per call of rmpc_solve_batch_static
+constexpr int kStaticHeaderInts = 64;                        // 256 bytes: [0] feasible count, [1] shifted count, [2] feasible head, [3] shifted head
+static __device__ __align__(256) int g_static_scratch[kStaticHeaderInts + 2 * kStaticMaxBatch];   // 131 328 bytes
+
+constexpr int kStaticMaxDevices = 64;
+struct StaticDevice {
+  bool ready;
+  int* scratch;          // device address of g_static_scratch on this device (cudaGetSymbolAddress; the symbol itself is a host-side stand-in)
+  int sm_count, bps, bps_sh;
+};
+static StaticDevice g_static_dev[kStaticMaxDevices];
+static std::mutex g_static_mu;
+
+// once per device, with that device current (the caller's current device); no allocation
+static int static_setup(int dev) {
+  StaticDevice& d = g_static_dev[dev];
+  if (d.ready) return 0;
+  void* ptr = nullptr;
+  CK(cudaGetSymbolAddress(&ptr, g_static_scratch));
+  d.scratch = static_cast<int*>(ptr);
+  const size_t smem = kSharedPerWarp * kWarps;
+  CK(cudaFuncSetAttribute(solve_kernel<I32::kFeasible>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CK(cudaFuncSetAttribute(solve_kernel<I32::kShifted>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.bps, solve_kernel<I32::kFeasible>, 32 * kWarps, smem));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.bps_sh, solve_kernel<I32::kShifted>, 32 * kWarps, smem));
+  CK(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+  if (d.bps < 1 || d.bps_sh < 1) { snprintf(g_err, sizeof g_err, "solve kernel does not fit on an SM (%zu B shared)", smem); return -1; }
+  d.ready = true;
+  return 0;
+}
+
+int rmpc_solve_batch_static(int B, const double* xinit, const double* x0, const double* params, double* z_out, double* action_out,
+                            const rmpc_info* info, const rmpc_options* opt, void* stream) {
+  if (!xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
+  if (B <= 0 || B > kStaticMaxBatch) {
+    snprintf(g_err, sizeof g_err, "rmpc_solve_batch_static: B=%d outside (0, %d] (the static scratch array holds two lists of %d problems)", B, kStaticMaxBatch, kStaticMaxBatch);
+    return -1;
+  }
+  rmpc_options o;
+  rmpc_default_options(&o);
+  if (opt) {
+    if (opt->precision != 0 || opt->hessian < 0 || opt->hessian > 1 || opt->control_mode < 0 || opt->control_mode > 1 || opt->creep_trigger < 0 || opt->stall_window < 0) {
+      snprintf(g_err, sizeof g_err, "option out of range");
+      return -1;
+    }
+    o = *opt;
+  }
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices) { snprintf(g_err, sizeof g_err, "device %d outside the static table", dev); return -1; }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (static_setup(dev)) return -1;
+  const StaticDevice& d = g_static_dev[dev];
+  cudaStream_t st = (cudaStream_t)stream;
+  SolveArgs a;
+  a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
+  a.p_bs = (long)M::N * M::NPAR; a.p_ss = (long)M::NPAR;
+  memset(&a.info, 0, sizeof a.info);
+  if (info) a.info = *info;
+  a.opt = to_core(o);
+  a.control_mode = o.control_mode;
+  int* q = d.scratch;
+  int* list = d.scratch + kStaticHeaderInts;
+  // the array keeps the last call's contents: counts and heads must start at zero; the lists are rewritten up to the new counts
+  CK(cudaMemsetAsync(q, 0, kStaticHeaderInts * sizeof(int), st));
+  {
+    const int warps_per_block = 8;
+    long blocks = ((long)B + warps_per_block - 1) / warps_per_block;
+    const long cap = (long)d.sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    classify_kernel<<<(unsigned)blocks, 32 * warps_per_block, 0, st>>>(B, a, q, list, kStaticMaxBatch);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  const long need = ((long)B + kWarps - 1) / kWarps;
+  const size_t smem = kSharedPerWarp * kWarps;
+  // one stream, no fork (no streams or events of a handle here): feasible starts, then the (rare) shifted starts
+  long grid = (long)d.bps * d.sm_count;
+  if (grid > need) grid = need;
+  solve_kernel<I32::kFeasible><<<(unsigned)grid, 32 * kWarps, smem, st>>>(B, a, list, q, q + 2);
+  g_launches++;
+  CK(cudaGetLastError());
+  grid = (long)d.bps_sh * d.sm_count;
+  if (grid > need) grid = need;
+  solve_kernel<I32::kShifted><<<(unsigned)grid, 32 * kWarps, smem, st>>>(B, a, list + kStaticMaxBatch, q + 1, q + 3);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int rmpc_static_max_batch(void) { return kStaticMaxBatch; }
+
 }  // extern "C"

@@ -41,7 +41,7 @@ class RmpcInfo(ctypes.Structure):
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
            "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_strided", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
-           "rmpc_set_params", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_launch_count"]
+           "rmpc_set_params", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_solve_batch_static", "rmpc_static_max_batch", "rmpc_launch_count"]
 
 
 class SolverError(RuntimeError):
@@ -78,6 +78,7 @@ def load_library(solver_dir: str) -> ctypes.CDLL:
     lib.rmpc_set_x0.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
     lib.rmpc_predict_obstacles.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
+    lib.rmpc_solve_batch_static.argtypes = ([ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo), ctypes.POINTER(RmpcOptions), ctypes.c_void_p])
     lib.rmpc_launch_count.restype = ctypes.c_long
     return lib
 
