@@ -516,7 +516,7 @@ def run_ours(args):
         b.sampler.stop()
         line = {"metric": "converged MPC solves/sec", "value": rec["value"], "unit": "converged solves/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64" if args.precision == 0 else "f64+f32", "data": "synthetic",
+                "vs_baseline": None, "dtype": {0: "f64", 1: "f32+f64"}[args.precision], "data": "synthetic",
                 "config": workload_config(args, args.workload, B, world),
                 "run": {"streams": nstreams, "l2": rec["l2"] + "; single-batch timing with L2 flushed (256 MB write)",
                         "note": "value needs several batches in flight (streams); roofline.one_batch_alone is what a closed loop, whose next step depends on this one, gets"},

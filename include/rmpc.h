@@ -44,7 +44,11 @@ typedef struct {
 typedef struct {
   int max_iter;     /* iteration cap, default 200 (FORCESPRO default) */
   int hessian;      /* 0 Gauss-Newton, 1 exact Lagrangian Hessian with Gauss-Newton fallback */
-  int precision;    /* 0: float64 throughout (the only mode of this build; any other value is rejected by rmpc_solve_batch) */
+  int precision;    /* 0 (default, the parity mode: the reference's generated code is all-double): float64 throughout.
+                       1: mixed — batches of more than 32 problems iterate in float32 while the barrier parameter is large
+                       (down to mu = 1e-4, loose tolerances), then a float64 kernel continues from that state to the
+                       tolerances below; a problem float32 cannot handle is solved in float64 from the caller's guess.
+                       Same exit flags and tolerances as 0; may stop in another local minimum of a non-convex problem */
   int control_mode; /* 0 "acc": action = u of stage 1; 1 "vel": action = z_2[nvar-2nu : nvar-nu] (mpcPlanner.py:275-278) */
   double tol_stat, tol_eq, tol_ineq, tol_comp;
   double mu0, mu_min, reg;

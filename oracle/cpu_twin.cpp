@@ -10,6 +10,7 @@
 // build: g++ -O3 -march=native -fopenmp -std=c++17 -shared -fPIC -I <solver_dir> -I robot_mpcs_b200/csrc
 #include <omp.h>
 #include <cstring>
+#include <vector>
 #include "model_traits.h"
 #include "rmpc_ipm.cuh"
 
@@ -17,26 +18,35 @@ using M = ModelTraits;
 
 template <class T>
 static void run(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
-                int* iters, double* resid, const rmpc::Options& opt) {
+                int* iters, double* resid, const rmpc::Options& opt, bool mixed) {
 #pragma omp parallel
   {
     auto* S = new rmpc::ProblemShared<M, T>();
-    T* p = new T[M::N * M::NPAR];
-    T* zin = new T[M::N * M::NVAR];
-    T* zo = new T[M::N * M::NVAR];
+    auto* Sf = new rmpc::ProblemShared<M, float>();
+    std::vector<float> hz(M::N * M::NVAR), hlam(M::N * M::NH);
     rmpc::Group<1> g{0};
 #pragma omp for schedule(dynamic, 8)
     for (int b = 0; b < B; ++b) {
-      for (int i = 0; i < M::N * M::NVAR; ++i) zin[i] = T(x0[size_t(b) * M::N * M::NVAR + i]);
-      for (int i = 0; i < M::N * M::NPAR; ++i) p[i] = T(params[size_t(b) * M::N * M::NPAR + i]);
-      T xi[M::NX];
-      for (int i = 0; i < M::NX; ++i) xi[i] = T(xinit[size_t(b) * M::NX + i]);
-      rmpc::ParamView<T> pv{p, M::NPAR, 1};
+      const double* xi = xinit + size_t(b) * M::NX;
+      const double* zin = x0 + size_t(b) * M::N * M::NVAR;
+      double* zo = z_out + size_t(b) * M::N * M::NVAR;
+      rmpc::ParamView<T, double> pv{params + size_t(b) * M::N * M::NPAR, M::NPAR, 1};
       rmpc::Info info;
-      auto* ipm = new rmpc::Ipm<M, T, 1>(g, *S, pv, opt);
-      ipm->solve(xi, zin, zo, info);
+      auto* ipm = new rmpc::Ipm<M, T, 1, double>(g, *S, pv, opt);
+      if (mixed) {   // precision 1: float32 iterations while the barrier parameter is large, float64 to finish (rmpc_ipm.cuh)
+        using If = rmpc::Ipm<M, float, 1, double>;
+        rmpc::ParamView<float, double> pvf{pv.base, M::NPAR, 1};
+        const rmpc::Options lo = If::lowp_options(opt);
+        auto* f = new If(g, *Sf, pvf, lo);
+        float hmu = 0.0f;
+        int hit = -1;
+        f->solve_lowp(xi, zin, hz.data(), hlam.data(), &hmu, &hit);
+        delete f;
+        if constexpr (sizeof(T) == 8) ipm->solve_resume(xi, zin, zo, hz.data(), hlam.data(), hmu, hit, info);
+      } else {
+        ipm->solve(xi, zin, zo, info);
+      }
       delete ipm;
-      for (int i = 0; i < M::N * M::NVAR; ++i) z_out[size_t(b) * M::N * M::NVAR + i] = double(zo[i]);
       exitflag[b] = info.exitflag;
       iters[b] = info.iters;
       if (resid) {
@@ -44,8 +54,7 @@ static void run(int B, const double* xinit, const double* x0, const double* para
         r[0] = info.obj; r[1] = info.res_stat; r[2] = info.res_eq; r[3] = info.res_ineq; r[4] = info.res_comp; r[5] = info.mu;
       }
     }
-    delete S;
-    delete[] p; delete[] zin; delete[] zo;
+    delete S; delete Sf;
   }
 }
 
@@ -54,7 +63,7 @@ const char* twin_name() { return M::NAME; }
 void twin_dims(int* d) { d[0] = M::N; d[1] = M::NX; d[2] = M::NU; d[3] = M::NVAR; d[4] = M::NPAR; d[5] = M::NH; }
 int twin_max_threads() { return omp_get_max_threads(); }
 
-// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg, delta, kappa, tau_min]; precision: 0 f64, 2 f32
+// opts: [max_iter, hessian, tol_stat, tol_eq, tol_ineq, tol_comp, mu0, mu_min, reg, delta, kappa, tau_min]; precision: 0 f64, 1 f32 then f64 (rmpc_options.precision = 1), 2 f32 throughout (experiments)
 int twin_solve_batch(int B, const double* xinit, const double* x0, const double* params, double* z_out, int* exitflag,
                      int* iters, double* resid, const double* opts, int nthreads, int precision) {
   rmpc::Options o = rmpc::default_options();
@@ -63,8 +72,8 @@ int twin_solve_batch(int B, const double* xinit, const double* x0, const double*
     o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8]; o.delta = opts[9]; o.kappa = opts[10]; o.tau_min = opts[11]; o.lm0 = opts[12]; o.lm_up = opts[13]; o.lm_down = opts[14]; o.lm_trigger = opts[15]; o.creep_trigger = opts[16]; o.creep_factor = opts[17]; o.stall_window = opts[18]; o.gn_hold_max = opts[19]; o.ls_optimistic = opts[20];
   }
   if (nthreads > 0) omp_set_num_threads(nthreads);
-  if (precision == 2) run<float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
-  else run<double>(B, xinit, x0, params, z_out, exitflag, iters, resid, o);
+  if (precision == 2) run<float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o, false);
+  else run<double>(B, xinit, x0, params, z_out, exitflag, iters, resid, o, precision == 1);
   return 0;
 }
 

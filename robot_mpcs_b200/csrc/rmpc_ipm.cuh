@@ -87,6 +87,11 @@ __device__ __noinline__ double warp_max(double v) {
   for (int o = 16; o > 0; o >>= 1) { const double w = __shfl_xor_sync(0xffffffffu, v, o); v = w > v ? w : v; }
   return v;
 }
+__device__ __noinline__ float warp_sumf(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
 __device__ __noinline__ float warp_maxf(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -96,6 +101,8 @@ template <> struct Group<32> {
   int lane;
   __device__ __forceinline__ void sync() const { __syncwarp(); }
   __device__ __forceinline__ double sum(double v) const { return warp_sum(v); }
+  __device__ __forceinline__ float sum(float v) const { return warp_sumf(v); }
+  __device__ __forceinline__ float bcast(float v, int src) const { return __shfl_sync(0xffffffffu, v, src); }
   __device__ __forceinline__ double max(double v) const { return warp_max(v); }
   __device__ __forceinline__ double min(double v) const { return -warp_max(-v); }
   __device__ __forceinline__ float max(float v) const { return warp_maxf(v); }
@@ -114,23 +121,24 @@ template <> struct Group<32> {
 };
 #endif
 
-// Parameter access: p(k, j) of one problem.
-template <class T>
+// Parameter access: p(k, j) of one problem.  TS is the type the parameters are stored in (the caller's float64 arrays), T
+// the type the solve computes in.
+template <class T, class TS = T>
 struct ParamView {
-  const T* base;
+  const TS* base;
   long stage_stride;  // elements between consecutive stages
   long elem_stride;   // elements between consecutive parameters
   RMPC_HD T get(int k, int j) const {
 #if defined(__CUDA_ARCH__) && defined(RMPC_PARAM_LOAD)
-    return RMPC_PARAM_LOAD(base + k * stage_stride + j * elem_stride);   // experiment: __ldcg / __ldcs / __ldg
+    return T(RMPC_PARAM_LOAD(base + k * stage_stride + j * elem_stride));   // experiment: __ldcg / __ldcs / __ldg
 #else
-    return base[k * stage_stride + j * elem_stride];
+    return T(base[k * stage_stride + j * elem_stride]);
 #endif
   }
 };
 
-template <class M, class T>
-RMPC_HD void load_params(const ParamView<T>& pv, int k, T* p) {
+template <class M, class T, class PV>
+RMPC_HD void load_params(const PV& pv, int k, T* p) {
   RMPC_UNROLL
   for (int j = 0; j < M::NPAR; ++j) p[j] = pv.get(k, j);
 }
@@ -150,14 +158,17 @@ template <class M> struct Dims {
   static constexpr int OFF1 = OFF0 - 2 * RV, OFFL = OFF0 - RV;
   static constexpr int LDF = (NVA % 2) ? NVA : NVA + 1;            // odd row stride of F / PAB: row- and column-wise accesses are conflict-free
   static constexpr int NQS0 = OFF0 + RV > 2 * M::NH ? OFF0 + RV : 2 * M::NH;
-  static constexpr int NQS1 = NQS0 + (NQS0 & 1);                   // even: what follows stays 16-byte aligned
   // In the stage-parallel phases lane k works on stage k, so the lanes of a warp access shared memory with the stage
-  // stride.  The stride (in doubles) is kept = 2 (mod 4): 16-byte aligned, conflict-free for 128-bit accesses and two-way
-  // for 64-bit ones.  A multiple of 16 puts every lane on the same bank (measured: 45 % of all shared wavefronts were
-  // conflicts with a 112-double stage, 10 % with 126).
-  static constexpr int STAGE0 = 2 * M::NVAR + NQS1 + DynS<M>::NABV + M::NX + 2;
-  static constexpr int STAGE1 = STAGE0 + (STAGE0 & 1);             // what alignas(16) rounds the struct to
-  static constexpr int NQS = NQS1 + ((STAGE1 % 4 == 2) ? 0 : 2);
+  // stride.  The stride is kept = 4 (mod 8) 32-bit words (float64: 2 (mod 4) doubles): 16-byte aligned, conflict-free for
+  // 128-bit accesses, two-way for 64-bit ones.  A multiple of 32 words puts every lane on the same bank (measured: 45 % of
+  // all shared wavefronts were conflicts with a 112-double stage, 6 % with 114).
+  template <class T> static constexpr int nqs() {
+    constexpr int per16 = 16 / int(sizeof(T));                       // elements per 16 bytes
+    constexpr int q1 = (NQS0 + per16 - 1) / per16 * per16;            // what follows Qs stays 16-byte aligned
+    constexpr int stage = 2 * M::NVAR + q1 + DynS<M>::NABV + M::NX + 2;
+    constexpr int words = (stage + per16 - 1) / per16 * per16 * int(sizeof(T)) / 4;   // alignas(16) rounds the struct up
+    return q1 + ((words % 8 == 4) ? 0 : per16);
+  }
 };
 
 template <class M, class T>
@@ -170,7 +181,7 @@ struct alignas(16) StageShared {
   // Everything before g0 is dead once phase 1 of the sweep has consumed it; K | kff0 | kff1 then reuse that space.
   // After the roll-out the same array is scratch for the line search: row values of the trial point in [0, NH), multiplier
   // steps in [NH, 2 NH).
-  T Qs[Dims<M>::NQS];
+  T Qs[Dims<M>::template nqs<T>()];
   T ABv[DynS<M>::NABV];      // z-dependent entries of [A B]
   T d[M::NX];                // Phi(z_k) - x_{k+1}
   T nu01[2];                 // adjoint of (X+, Y+) from the previous sweep (diff-drive curvature)
@@ -185,7 +196,7 @@ struct alignas(16) StageShared {
 
 template <class M, class T>
 struct ProblemShared {
-  static_assert(sizeof(T) != 8 || (sizeof(StageShared<M, T>) / 8) % 4 == 2, "stage stride must be 2 (mod 4) doubles");
+  static_assert((sizeof(StageShared<M, T>) / 4) % 8 == 4, "stage stride must be 4 (mod 8) words");
   StageShared<M, T> st[M::N];
   T PAB[Dims<M>::RX * Dims<M>::LDF];   // P_{k+1} [A B | d-term | p1 | nu] of the stage being processed (compact variables)
   T F[Dims<M>::RV * Dims<M>::LDF];     // [Q | g0 | g1 | gl] + [A B]' PAB, every entry valid (the matrix part is symmetric up to rounding)
@@ -198,7 +209,7 @@ struct Red {  // what phase A + the sweep measure at the current iterate
 };
 
 // ------------------------------------------------------------------------------------------------
-template <class M, class T, int G>
+template <class M, class T, int G, class TS = T>
 struct Ipm {
   static constexpr int NX = M::NX, NU = M::NU, NV = M::NVAR, NH = M::NH, N = M::N, NQ = M::NQ;
   static constexpr int NGEO1 = M::NGEO > 0 ? M::NGEO : 1;
@@ -209,7 +220,7 @@ struct Ipm {
 
   const Group<G>& g;
   ProblemShared<M, T>& S;
-  const ParamView<T>& pv;
+  const ParamView<T, TS>& pv;
   const Options& opt;
 
   // per-lane state of the stages this lane owns
@@ -217,7 +228,7 @@ struct Ipm {
   float sh[SLOTS][NH];  // shifts of the rows that started infeasible; referenced only by the <SH = true> instantiations below
   T Gg[SLOTS][NGEO1][NQ];
 
-  RMPC_HD Ipm(const Group<G>& g_, ProblemShared<M, T>& S_, const ParamView<T>& pv_, const Options& o_) : g(g_), S(S_), pv(pv_), opt(o_) {}
+  RMPC_HD Ipm(const Group<G>& g_, ProblemShared<M, T>& S_, const ParamView<T, TS>& pv_, const Options& o_) : g(g_), S(S_), pv(pv_), opt(o_) {}
 
 
   // ---- A: stage-parallel derivatives ----------------------------------------------------------
@@ -585,12 +596,12 @@ struct Ipm {
   //   kShifted  the others: iterate<true> until the last shift is gone, then iterate<false>
   // The CUDA host code classifies a batch ONCE (classify_kernel -> two index lists) and runs the last two as two
   // kernels side by side, each on its own list, so that the common case runs the smaller code.
-  static constexpr int kAll = 0, kFeasible = 1, kShifted = 2;
+  static constexpr int kAll = 0, kFeasible = 1, kShifted = 2, kResume = 3;   // kResume: solve_resume (mixed precision, below)
 
-  RMPC_HD void load_guess(const T* xinit, const T* z_in) {
-    for (int e = g.lane; e < N * NV; e += G) S.st[e / NV].z[e % NV] = z_in[e];
+  RMPC_HD void load_guess(const TS* xinit, const TS* z_in) {
+    for (int e = g.lane; e < N * NV; e += G) S.st[e / NV].z[e % NV] = T(z_in[e]);
     g.sync();
-    for (int e = g.lane; e < NX; e += G) S.st[0].z[e] = xinit[e];
+    for (int e = g.lane; e < NX; e += G) S.st[0].z[e] = T(xinit[e]);
     for (int e = g.lane; e < N; e += G) { S.st[e].nu01[0] = T(0); S.st[e].nu01[1] = T(0); }
     g.sync();
   }
@@ -614,7 +625,7 @@ struct Ipm {
   }
 
   template <int MODE = 0>
-  RMPC_HD void solve(const T* xinit, const T* z_in, T* z_out, Info& info) {
+  RMPC_HD void solve(const TS* xinit, const TS* z_in, TS* z_out, Info& info) {
     // initial point: z from the guess, x_1 = xinit
     load_guess(xinit, z_in);
     T mu = T(opt.mu0);
@@ -667,6 +678,115 @@ struct Ipm {
     finish(L, z_out, info);
   }
 
+
+  // ---- mixed precision (rmpc_options.precision = 1): the iteration runs in float32 while the barrier parameter is large
+  // and hands its state (z, lambda, mu, iteration count) to the float64 build of the same iteration, which finishes the
+  // solve to the caller's tolerances.  Late iterations need float64: active rows reach lambda/s ~ 1e9 and slacks fall below
+  // the rounding of a float32 row value; early iterations do not.  The reference's generated code is all-double
+  // (models/mpcModel.py:110-126 sets no precision option), so precision 0 stays the parity mode.
+  //
+  // solve_lowp: the float32 part (T = float).  hit = iterations done, or -1: start over in float64 (the float32 iteration
+  // broke down, or the guess sits on a pole).  The caller passes options with the tolerances float32 can reach (lowp_options).
+  static RMPC_HD Options lowp_options(Options o) {
+    o.tol_stat = 1e-2; o.tol_eq = 1e-4; o.tol_ineq = 1e-4; o.tol_comp = 1e-3; o.mu_min = 1e-4;
+    return o;
+  }
+
+  RMPC_HD void solve_lowp(const TS* xinit, const TS* z_in, float* hz, float* hlam, float* hmu, int* hit) {
+    load_guess(xinit, z_in);
+    T mu = T(opt.mu0);
+    bool pole0 = false;
+    RMPC_UNROLL
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      const int k = g.lane + G * sl;
+      if (k < N) {
+        T p[M::NPAR];
+        load_params<M, T>(pv, k, p);
+        StageVal<M, T> sv;
+        stage_values<M, T>(S.st[k].z, p, sv);
+        pole0 = pole0 || sv.pole;
+        RMPC_UNROLL
+        for (int r = 0; r < NH; ++r) {
+          s[sl][r] = sv.h[r];
+          lam[sl][r] = mu * trcp(sv.h[r]);
+          pole0 = pole0 || !(sv.h[r] > T(0));   // float32 rounding of a row the classification (float64) found >= delta: leave it to float64
+        }
+      }
+    }
+    Info info;
+    info.exitflag = 0;
+    Loop L;
+    L.mu = mu; L.it = 0;
+    L.so.f = L.so.res_stat = L.so.res_eq = L.so.comp_max = L.so.shift_max = T(0);
+    if (g.any(pole0)) info.exitflag = -8;
+    else iterate<false>(L, info);
+    const bool go_on = info.exitflag >= 0;
+    if (go_on) {
+      for (int e = g.lane; e < N * NV; e += G) hz[e] = float(S.st[e / NV].z[e % NV]);
+      RMPC_UNROLL
+      for (int sl = 0; sl < SLOTS; ++sl) {
+        const int k = g.lane + G * sl;
+        if (k < N) {
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r) hlam[k * NH + r] = float(lam[sl][r]);
+        }
+      }
+    }
+    if (g.lane == 0) { *hmu = float(L.mu); *hit = go_on ? (L.it > opt.max_iter ? opt.max_iter : L.it) : -1; }
+  }
+
+  // solve_resume: the float64 part (T = double, no shift code).  At most two passes through the one copy of the float64
+  // iteration: from the handed-over state, and — if there is none, or it led nowhere — from the caller's guess, as
+  // precision 0 would.
+  RMPC_HD void solve_resume(const TS* xinit, const TS* z_in, TS* z_out, const float* hz, const float* hlam, float hmu, int hit, Info& info) {
+    Loop L;
+    for (int pass = hit >= 0 ? 0 : 1; pass < 2; ++pass) {
+      const bool resume = pass == 0;
+      if (resume) {
+        for (int e = g.lane; e < N * NV; e += G) S.st[e / NV].z[e % NV] = T(hz[e]);
+        g.sync();
+        for (int e = g.lane; e < NX; e += G) S.st[0].z[e] = T(xinit[e]);   // x_1 = xinit exactly
+        for (int e = g.lane; e < N; e += G) { S.st[e].nu01[0] = T(0); S.st[e].nu01[1] = T(0); }
+        g.sync();
+      } else {
+        load_guess(xinit, z_in);
+      }
+      const T mu = resume ? T(hmu) : T(opt.mu0);
+      bool pole0 = false;
+      RMPC_UNROLL
+      for (int sl = 0; sl < SLOTS; ++sl) {
+        const int k = g.lane + G * sl;
+        if (k < N) {
+          T p[M::NPAR];
+          load_params<M, T>(pv, k, p);
+          StageVal<M, T> sv;
+          stage_values<M, T>(S.st[k].z, p, sv);
+          pole0 = pole0 || sv.pole;
+          RMPC_UNROLL
+          for (int r = 0; r < NH; ++r) {
+            if (resume) {
+              const T lr = tmax(T(hlam[k * NH + r]), T(1e-30));
+              // the slack is the row's own value; where float32 rounding of z has eaten a tiny slack, a tenth of the centred
+              // value mu / lambda stands in until the first accepted step re-evaluates the row
+              s[sl][r] = tmax(sv.h[r], T(0.1) * mu * trcp(lr));
+              lam[sl][r] = lr;
+            } else {
+              s[sl][r] = sv.h[r];
+              lam[sl][r] = mu * trcp(sv.h[r]);
+            }
+          }
+        }
+      }
+      info.exitflag = 0;
+      L = Loop();
+      L.mu = mu; L.it = resume ? hit : 0;
+      L.so.f = L.so.res_stat = L.so.res_eq = L.so.comp_max = L.so.shift_max = T(0);
+      if (g.any(pole0)) { info.exitflag = -8; L.it = opt.max_iter + 1; }
+      iterate<false>(L, info);
+      if (info.exitflag >= 0) break;
+    }
+    finish(L, z_out, info);
+  }
 
   // Runs iterations until the solve ends (returns true) or, for SH, until no row of the problem is shifted any more.
   template <bool SH>
@@ -894,9 +1014,9 @@ struct Ipm {
     return !handover;
   }
 
-  RMPC_HD void finish(const Loop& L, T* z_out, Info& info) {
+  RMPC_HD void finish(const Loop& L, TS* z_out, Info& info) {
     if (z_out)
-      for (int e = g.lane; e < N * NV; e += G) z_out[e] = S.st[e / NV].z[e % NV];
+      for (int e = g.lane; e < N * NV; e += G) z_out[e] = TS(S.st[e / NV].z[e % NV]);
     // The NLP of the reference carries -100 <= z <= 100 on every stage variable (models/mpcModel.py:23-28,98-104).  The
     // box is not part of the barrier problem solved here (it is never active in a sensible scenario, and 2 nvar more rows
     // per stage would cost every solve); a converged point that touches or leaves it is not a solution of the

@@ -44,9 +44,15 @@ RMPC_HD float fdiv_approx(float a, float b) {  // 2 ulp: for ratios that only ca
 RMPC_HD float tsqrt(float a) { return sqrtf(a); }
 RMPC_HD double tsqrt(double a) { return sqrt(a); }
 RMPC_HD float tlog(float a) { return logf(a); }
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ float trcp(float a) { return __frcp_rn(a); }
+__device__ __forceinline__ float trsqrt(float a) { return rsqrtf(a); }
+__device__ __forceinline__ void tsincos(float a, float* s, float* c) { sincosf(a, s, c); }
+#else
 RMPC_HD float trcp(float a) { return 1.0f / a; }
 RMPC_HD float trsqrt(float a) { return 1.0f / sqrtf(a); }
 RMPC_HD void tsincos(float a, float* s, float* c) { *s = sinf(a); *c = cosf(a); }
+#endif
 #if defined(__CUDA_ARCH__)
 // Device: the libm expansions of sincos / log are ~150 / ~60 instructions each; one out-of-line copy keeps the solve
 // kernel inside the instruction cache.  Reciprocal and reciprocal square root: the 64-bit MUFU seed (rcp/rsqrt

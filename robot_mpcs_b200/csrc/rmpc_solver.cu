@@ -63,6 +63,9 @@ struct Slot {
   cudaStream_t side;    // the kernel for shifted starts runs here, forked from and joined to the caller's stream
   cudaEvent_t ev_fork, ev_join, ev_done;
   bool used;
+  // mixed precision (options.precision = 1): what the float32 kernel hands to the float64 kernel, per problem of the batch
+  float *hz, *hlam, *hmu;   // z [N][nvar], lambda [N][nh], mu
+  int* hit;                 // iterations done in float32, -1 = solve from the caller's guess in float64
 };
 
 struct LatencyGraph {   // captured H2D -> single-launch solve -> D2H for one small batch size (rmpc_solve_batch_host)
@@ -78,6 +81,7 @@ struct rmpc_solver {
   Slot slot[kSlots];
   int next_slot;
   int blocks_per_sm, blocks_per_sm_sh, blocks_per_sm_all, sm_count;
+  int bps_lowp, bps_resume;   // resident blocks per SM of the two kernels of a mixed-precision solve
   size_t smem_bytes;  // dynamic shared memory per block
   // device staging for the host entry points: one packed input block and one packed output block
   double* d_in;         // xinit | x0 | params
@@ -109,7 +113,9 @@ static_assert(kWarps >= 1, "one problem does not fit into the shared memory of a
 #ifndef RMPC_MIN_BLOCKS
 #define RMPC_MIN_BLOCKS 1   // resident blocks per SM the register allocation must allow
 #endif
+struct Handoff { const float *z, *lam, *mu; const int* it; };
 struct SolveArgs {
+  Handoff ho;        // mixed precision only: state left by the float32 pass
   const double *xinit, *x0, *params;
   long p_bs, p_ss;   // elements between the parameter blocks of consecutive problems / stages (reference layout: N*npar, npar)
   double *z_out, *action;
@@ -191,7 +197,7 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__
     int b = 0;
     if (g.lane == 0) {
       b = atomicAdd(head, 1);
-      if (MODE != I32::kAll) b = b < n ? list[b] : B;
+      if (MODE != I32::kAll) b = b < n ? list[b] : B;   // kFeasible, kShifted, kResume: the problems of a list
     }
     b = __shfl_sync(0xffffffffu, b, 0);
     if (b >= B) {
@@ -203,10 +209,46 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__
     Info inf;
     {
       I32 ipm(g, S, pv, a.opt);
-      ipm.template solve<MODE>(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR,
-                               a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
+      if constexpr (MODE == I32::kResume)
+        ipm.solve_resume(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR, a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr,
+                         a.ho.z + (size_t)b * M::N * M::NVAR, a.ho.lam + (size_t)b * M::N * M::NH, a.ho.mu[b], a.ho.it[b], inf);
+      else
+        ipm.template solve<MODE>(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR,
+                                 a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr, inf);
     }
     write_outputs(a, S, g.lane, b, inf);
+    __syncwarp();
+  }
+}
+
+// Mixed precision, pass 1: the iteration in float32 (rmpc_ipm.cuh solve_lowp) on the feasible list, while the barrier
+// parameter is large; the state goes to global memory, and solve_kernel<kResume> (float64) finishes the solve.  Half the
+// shared memory and fewer registers than the float64 kernel: more problems per SM, and shorter dependent chains.
+#ifndef RMPC_LOWP_MIN_BLOCKS
+#define RMPC_LOWP_MIN_BLOCKS 10
+#endif
+using SharedF = ProblemShared<M, float>;
+constexpr size_t kSharedFPerWarp = (sizeof(SharedF) + 15) / 16 * 16;
+__global__ void __launch_bounds__(32, RMPC_LOWP_MIN_BLOCKS)
+lowp_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__ list, const int* __restrict__ count, int* __restrict__ head,
+            float* __restrict__ hz, float* __restrict__ hlam, float* __restrict__ hmu, int* __restrict__ hit) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SharedF& S = *reinterpret_cast<SharedF*>(smem_raw);
+  Group<32> g{int(threadIdx.x & 31)};
+  using IF = Ipm<M, float, 32, double>;
+  const Options lo = IF::lowp_options(a.opt);
+  const int n = *count;
+  for (;;) {
+    int b = 0;
+    if (g.lane == 0) { b = atomicAdd(head, 1); b = b < n ? list[b] : B; }
+    b = __shfl_sync(0xffffffffu, b, 0);
+    if (b >= B) break;
+    const ParamView<float, double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
+    {
+      IF ipm(g, S, pv, lo);
+      ipm.solve_lowp(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR, hz + (size_t)b * M::N * M::NVAR,
+                     hlam + (size_t)b * M::N * M::NH, hmu + b, hit + b);
+    }
     __syncwarp();
   }
 }
@@ -309,7 +351,7 @@ void rmpc_default_options(rmpc_options* o) {
 static void free_all(rmpc_solver* s) {
   for (int i = 0; i < kSlots; ++i) {
     Slot& sl = s->slot[i];
-    cudaFree(sl.q); cudaFree(sl.list);
+    cudaFree(sl.q); cudaFree(sl.list); cudaFree(sl.hz); cudaFree(sl.hlam); cudaFree(sl.hmu); cudaFree(sl.hit);
     if (sl.side) cudaStreamDestroy(sl.side);
     if (sl.ev_fork) cudaEventDestroy(sl.ev_fork);
     if (sl.ev_join) cudaEventDestroy(sl.ev_join);
@@ -350,7 +392,7 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   };
   for (int i = 0; i < kSlots; ++i) {
     Slot& sl = s->slot[i];
-    if ((e = cudaMalloc(&sl.q, sizeof(int) * 4)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc(&sl.q, sizeof(int) * 8)) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaMalloc(&sl.list, sizeof(int) * 2 * (size_t)max_batch)) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaStreamCreateWithFlags(&sl.side, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaEventCreateWithFlags(&sl.ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
@@ -369,6 +411,12 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
       (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_sh, solve_kernel<I32::kShifted>, 32 * kWarps, smem)) != cudaSuccess ||
       (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_all, solve_kernel<I32::kAll>, 32 * kWarps, smem)) != cudaSuccess)
     return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor", e);
+  if ((e = cudaFuncSetAttribute(solve_kernel<I32::kResume>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(lowp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSharedFPerWarp)) != cudaSuccess)
+    return fail("cudaFuncSetAttribute(shared memory, mixed precision)", e);
+  if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->bps_resume, solve_kernel<I32::kResume>, 32 * kWarps, smem)) != cudaSuccess ||
+      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->bps_lowp, lowp_kernel, 32, kSharedFPerWarp)) != cudaSuccess)
+    return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor(mixed precision)", e);
   if (const char* cap = getenv("RMPC_MAX_BLOCKS_PER_SM")) {  // experiment knob: fewer problems in flight per SM
     const int c = atoi(cap);
     if (c > 0 && c < s->blocks_per_sm) s->blocks_per_sm = c;
@@ -417,6 +465,7 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* o) {
 static SolveArgs make_args(const rmpc_solver* s, const double* xinit, const double* x0, const double* params, long p_bs, long p_ss,
                            double* z_out, double* action_out, const rmpc_info* info) {
   SolveArgs a;
+  a.ho = Handoff{nullptr, nullptr, nullptr, nullptr};
   a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
   a.p_bs = p_bs; a.p_ss = p_ss;
   memset(&a.info, 0, sizeof a.info);
@@ -426,15 +475,65 @@ static SolveArgs make_args(const rmpc_solver* s, const double* xinit, const doub
   return a;
 }
 
+// options.precision = 1: classification as usual; shifted starts go to the float64 kernel on the side stream; the feasible
+// list is worked through twice on the caller's stream, in float32 (lowp_kernel) and then in float64 (solve_kernel<kResume>).
+static int launch_solve_mixed(rmpc_solver* s, int B, SolveArgs a, cudaStream_t st) {
+  static_assert(kWarps == 1, "the mixed-precision kernels are one-warp blocks");
+  Slot& sl = s->slot[s->next_slot];
+  s->next_slot = (s->next_slot + 1) % kSlots;
+  if (!sl.hz) {   // first mixed-precision call on this slot
+    const size_t mb = (size_t)s->max_batch;
+    CK(cudaMalloc(&sl.hz, sizeof(float) * mb * M::N * M::NVAR));
+    CK(cudaMalloc(&sl.hlam, sizeof(float) * mb * M::N * M::NH));
+    CK(cudaMalloc(&sl.hmu, sizeof(float) * mb));
+    CK(cudaMalloc(&sl.hit, sizeof(int) * mb));
+  }
+  if (sl.used) CK(cudaStreamWaitEvent(st, sl.ev_done, 0));
+  sl.used = true;
+  a.ho = Handoff{sl.hz, sl.hlam, sl.hmu, sl.hit};
+  CK(cudaMemsetAsync(sl.q, 0, 8 * sizeof(int), st));
+  {
+    const int warps_per_block = 8;
+    long blocks = ((long)B + warps_per_block - 1) / warps_per_block;
+    const long cap = (long)s->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    classify_kernel<<<(unsigned)blocks, 32 * warps_per_block, 0, st>>>(B, a, sl.q, sl.list, s->max_batch);
+    g_launches++;
+    CK(cudaGetLastError());
+  }
+  CK(cudaEventRecord(sl.ev_fork, st));
+  CK(cudaStreamWaitEvent(sl.side, sl.ev_fork, 0));
+  long grid = (long)s->blocks_per_sm_sh * s->sm_count;
+  if (grid > B) grid = B;
+  solve_kernel<I32::kShifted><<<(unsigned)grid, 32, s->smem_bytes, sl.side>>>(B, a, sl.list + s->max_batch, sl.q + 1, sl.q + 3);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(sl.ev_join, sl.side));
+  grid = (long)s->bps_lowp * s->sm_count;
+  if (grid > B) grid = B;
+  lowp_kernel<<<(unsigned)grid, 32, kSharedFPerWarp, st>>>(B, a, sl.list, sl.q, sl.q + 2, sl.hz, sl.hlam, sl.hmu, sl.hit);
+  g_launches++;
+  CK(cudaGetLastError());
+  grid = (long)s->bps_resume * s->sm_count;
+  if (grid > B) grid = B;
+  solve_kernel<I32::kResume><<<(unsigned)grid, 32, s->smem_bytes, st>>>(B, a, sl.list, sl.q, sl.q + 4);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamWaitEvent(st, sl.ev_join, 0));
+  CK(cudaEventRecord(sl.ev_done, st));
+  return 0;
+}
+
 // the launches of one batched solve on stream `st`; the caller holds s->mu and has set the device
 static int launch_solve(rmpc_solver* s, int B, const SolveArgs& a, cudaStream_t st) {
+  if (s->opt.precision == 1 && B > kSmallBatch) return launch_solve_mixed(s, B, a, st);   // small batches (latency path): float64 throughout
   Slot& sl = s->slot[s->next_slot];
   s->next_slot = (s->next_slot + 1) % kSlots;
   if (sl.used) CK(cudaStreamWaitEvent(st, sl.ev_done, 0));   // the call that used this slot kSlots calls ago (any stream) has finished
   sl.used = true;
   const long need = ((long)B + kWarps - 1) / kWarps;
   if (B <= kSmallBatch) {   // one launch: classification inside the solve
-    CK(cudaMemsetAsync(sl.q, 0, 4 * sizeof(int), st));
+    CK(cudaMemsetAsync(sl.q, 0, 8 * sizeof(int), st));
     long grid = (long)s->blocks_per_sm_all * s->sm_count;
     if (grid > need) grid = need;
     solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, st>>>(B, a, nullptr, nullptr, sl.q + 2);
@@ -443,7 +542,7 @@ static int launch_solve(rmpc_solver* s, int B, const SolveArgs& a, cudaStream_t 
     CK(cudaEventRecord(sl.ev_done, st));
     return 0;
   }
-  CK(cudaMemsetAsync(sl.q, 0, 4 * sizeof(int), st));
+  CK(cudaMemsetAsync(sl.q, 0, 8 * sizeof(int), st));
   {
     const int warps_per_block = 8;
     long blocks = ((long)B + warps_per_block - 1) / warps_per_block;
@@ -481,7 +580,6 @@ int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x
 static int check_solve_args(const rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params) {
   if (!s || !xinit || !x0 || !params) { snprintf(g_err, sizeof g_err, "null argument"); return -1; }
   if (B <= 0 || B > s->max_batch) { snprintf(g_err, sizeof g_err, "B=%d outside (0, max_batch=%d]", B, s->max_batch); return -1; }
-  if (s->opt.precision != 0) { snprintf(g_err, sizeof g_err, "precision %d is not available in this build (float64 only)", s->opt.precision); return -1; }
   return 0;
 }
 
@@ -783,6 +881,7 @@ int rmpc_solve_batch_static(int B, const double* xinit, const double* x0, const 
   const StaticDevice& d = g_static_dev[dev];
   cudaStream_t st = (cudaStream_t)stream;
   SolveArgs a;
+  a.ho = Handoff{nullptr, nullptr, nullptr, nullptr};
   a.xinit = xinit; a.x0 = x0; a.params = params; a.z_out = z_out; a.action = action_out;
   a.p_bs = (long)M::N * M::NPAR; a.p_ss = (long)M::NPAR;
   memset(&a.info, 0, sizeof a.info);

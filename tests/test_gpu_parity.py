@@ -255,9 +255,8 @@ def test_options_roundtrip_and_iteration_bounds(built):
     with pytest.raises(SolverError):
         solver.set_options(stall_window=-1)
     assert solver.options()["stall_window"] == 25          # a refused set leaves the handle's options as they were
-    solver.set_options(precision=1)                        # mixed precision is not in this build: refused at solve time
     with pytest.raises(SolverError):
-        solver.solve_batch(d["xinit"], d["x0"], d["params"])
+        solver.set_options(precision=2)                    # 0 = float64, 1 = float32 then float64; nothing else
 
 
 def test_device_reciprocals(built):
