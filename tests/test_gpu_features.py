@@ -344,3 +344,34 @@ def test_mixed_precision_against_the_fixtures_and_float64(built, name):
         assert e1[b] == 1
         same += bool(np.abs(z1[b] - zo).max() / np.abs(zo).max() < 1e-4 and abs(float(r1["obj"][b]) - c["obj"]) <= 1e-5 * abs(c["obj"]))
     assert same >= (FIXTURES[name] - 0.05) * valid, (name, same, valid)
+
+
+def test_closed_loop_in_vel_mode_follows_its_own_plan(built):
+    """rollout.closed_loop with control_mode vel: the velocity action is turned back into the input that realises it, so the
+    plant lands on the plan's own stage-2 state, and the velocity limits hold along the whole run."""
+    import torch
+    from robot_mpcs_b200.planner.mpcPlanner import MPCPlanner
+    from robot_mpcs_b200.rollout import closed_loop
+    from robot_mpcs_b200.utils.utils import parse_setup
+    B, T = 64, 25
+    setup = parse_setup(os.path.join(CONFIG, "boxerVelMpc.yaml"))["mpc"]
+    setup["initialization"] = "previous_plan"
+    pm = _pm("boxerVel_n3_01_H15_noSlack")
+    s = sc.boxer_vel(pm, B, seed=11)
+    pl = MPCPlanner("boxerVel", SOLVERS + os.sep, batch_size=B, device_resident=True, **setup)
+    pl.concretize(); pl.reset()
+    pl._params3[:] = _dev(s["params"])
+    err, vmax = [], []
+
+    def on_step(t, x, z, flag):
+        ok = flag == 1
+        err.append((z[ok, 1, :8] - x[ok]).abs().max())
+        vmax.append(torch.stack([x[:, 6].max(), x[:, 7].abs().max()]))
+
+    goal = _dev(s["params"][:, 0, pm["goal"]])
+    r = closed_loop(pl, _dev(s["xinit"]), goal, T, epsilon=0.3, on_step=on_step)
+    assert float(torch.stack(err).max()) < 1e-8
+    vm = torch.stack(vmax).max(0).values
+    assert float(vm[0]) <= 1.0 + 1e-6 and float(vm[1]) <= 1.0 + 1e-6
+    d0 = torch.linalg.norm(_dev(s["xinit"])[:, :2] - goal[:, :2], dim=1)
+    assert float((d0 - r["goal_distance"]).mean()) > 1.0 and int(r["failures"].sum()) <= 2
