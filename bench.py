@@ -30,6 +30,7 @@ sys.path.insert(0, ROOT)
 from robot_mpcs_b200 import scenarios as sc  # noqa: E402
 
 SOLVERS = os.path.join(ROOT, "robot_mpcs_b200", "solvers")
+LIB_DIR = os.environ.get("RMPC_VARIANT_DIR")   # experiments: directory of alternative lib<solver>.so builds (scripts/build_variant.sh)
 
 # name -> (solver dir, generator, default batch, F_iter flop/iteration (SURVEY §8d convention), stage-invariant parameters?, description)
 WORKLOADS = {
@@ -283,7 +284,7 @@ class Bench:
     def solver(self, workload, B):
         from robot_mpcs_b200.planner.solver import Solver
         a = self.args
-        s = Solver.from_directory(os.path.join(SOLVERS, WORKLOADS[workload][0]), device=self.local_rank, max_batch=B)
+        s = Solver.from_directory(os.path.join(SOLVERS, WORKLOADS[workload][0]), device=self.local_rank, max_batch=B, lib_dir=LIB_DIR)
         s.set_options(precision=a.precision, hessian=a.hessian, stall_window=a.stall_window)
         return s
 

@@ -26,6 +26,16 @@
 #include <stdio.h>
 #endif
 
+// Loops over the stages a lane owns (SLOTS = ceil(N / G)) stay rolled on the device.  With one stage per lane the loop has
+// one trip and disappears; with two (N > 32) the code of every stage-parallel phase exists once instead of twice, at the
+// price of indexing the per-lane state dynamically (local memory instead of registers that spilled anyway).  Measured on
+// the N = 40 model (B200, r2m): kernel 167 -> 110 KB, 366 k -> 424 k solves/s.  -DRMPC_UNROLL_SLOTS restores the unrolled form.
+#if defined(__CUDA_ARCH__) && !defined(RMPC_UNROLL_SLOTS)
+#define RMPC_UNROLL_SL _Pragma("unroll 1")
+#else
+#define RMPC_UNROLL_SL RMPC_UNROLL
+#endif
+
 namespace rmpc {
 
 struct Options {
@@ -162,10 +172,21 @@ template <class M> struct Dims {
   // stride.  The stride is kept = 4 (mod 8) 32-bit words (float64: 2 (mod 4) doubles): 16-byte aligned, conflict-free for
   // 128-bit accesses, two-way for 64-bit ones.  A multiple of 32 words puts every lane on the same bank (measured: 45 % of
   // all shared wavefronts were conflicts with a 112-double stage, 6 % with 114).
+  // The multipliers and slacks of a stage live in shared memory (2 NH values per stage) instead of in the registers of the
+  // lane that owns the stage, unless the horizon needs two stages per lane (N > 32), where the extra shared memory costs
+  // more in resident problems than it saves.  B200, r2n/r2o A/B (registers -> shared): panda 436 k -> 489 k solves/s and
+  // B = 1 latency 1.27 -> 0.88 ms; pointRobot 3.33 M -> 3.58 M; boxer N = 30 743 k -> 758 k, latency 1.11 -> 0.90 ms;
+  // boxer N = 40 424 k -> 399 k (kept in registers / local memory).  -DRMPC_STATE_SH=0/1 forces either form.
+#if defined(RMPC_STATE_SH)
+  static constexpr bool STATE_SH = RMPC_STATE_SH != 0;
+#else
+  static constexpr bool STATE_SH = M::N <= 32 || M::NH >= 24;
+#endif
+  static constexpr int NLS = STATE_SH ? 2 * M::NH : 2;
   template <class T> static constexpr int nqs() {
     constexpr int per16 = 16 / int(sizeof(T));                       // elements per 16 bytes
     constexpr int q1 = (NQS0 + per16 - 1) / per16 * per16;            // what follows Qs stays 16-byte aligned
-    constexpr int stage = 2 * M::NVAR + q1 + DynS<M>::NABV + M::NX + 2;
+    constexpr int stage = 2 * M::NVAR + q1 + DynS<M>::NABV + M::NX + 2 + NLS;
     constexpr int words = (stage + per16 - 1) / per16 * per16 * int(sizeof(T)) / 4;   // alignas(16) rounds the struct up
     return q1 + ((words % 8 == 4) ? 0 : per16);
   }
@@ -185,6 +206,7 @@ struct alignas(16) StageShared {
   T ABv[DynS<M>::NABV];      // z-dependent entries of [A B]
   T d[M::NX];                // Phi(z_k) - x_{k+1}
   T nu01[2];                 // adjoint of (X+, Y+) from the previous sweep (diff-drive curvature)
+  T ls[Dims<M>::NLS];        // STATE_SH models: lambda[NH] | s[NH] of this stage (2 unused entries otherwise)
   RMPC_HD T g0(int c) const { return Qs[Dims<M>::OFF0 + c]; }
   RMPC_HD T& K(int l, int c) { return Qs[l * Dims<M>::RX + c]; }
   RMPC_HD T K(int l, int c) const { return Qs[l * Dims<M>::RX + c]; }
@@ -224,7 +246,10 @@ struct Ipm {
   const Options& opt;
 
   // per-lane state of the stages this lane owns
-  T lam[SLOTS][NH], s[SLOTS][NH];
+  static constexpr bool STATE_SH = Dims<M>::STATE_SH;
+  T lam_r[SLOTS][STATE_SH ? 1 : NH], s_r[SLOTS][STATE_SH ? 1 : NH];
+  RMPC_HD T& LAM(int sl, int k, int r) { if constexpr (STATE_SH) return S.st[k].ls[r]; else return lam_r[sl][r]; }
+  RMPC_HD T& SLK(int sl, int k, int r) { if constexpr (STATE_SH) return S.st[k].ls[NH + r]; else return s_r[sl][r]; }
   float sh[SLOTS][NH];  // shifts of the rows that started infeasible; referenced only by the <SH = true> instantiations below
   T Gg[SLOTS][NGEO1][NQ];
 
@@ -238,7 +263,7 @@ struct Ipm {
     T f = T(0), theta = T(0), res_eq = T(0), msum = T(0), smin = T(1e300);
     float cmin = 3e38f, cmax = 0.0f, shmax = 0.0f;  // only compared with tolerances: single precision is enough
     bool pole = false;
-    RMPC_UNROLL
+    RMPC_UNROLL_SL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
       if (k < N) {
@@ -252,7 +277,7 @@ struct Ipm {
         T rho[NGEO1], kappa[NGEO1];
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
-          const T sr = s[sl][r], lr = lam[sl][r];
+          const T sr = SLK(sl, k, r), lr = LAM(sl, k, r);
           y1[r] = trcp(sr);
           sig[r] = lr * y1[r];
           lacc.mul(sr);
@@ -266,10 +291,10 @@ struct Ipm {
         if constexpr (SH) {  // a slack this small next to its shift cannot recover
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r)
-            if (sh[sl][r] > 0.0f) { smin = tmin(smin, s[sl][r] - T(1e-6f * sh[sl][r])); theta += T(sh[sl][r]); }
+            if (sh[sl][r] > 0.0f) { smin = tmin(smin, SLK(sl, k, r) - T(1e-6f * sh[sl][r])); theta += T(sh[sl][r]); }
         }
         RMPC_UNROLL
-        for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -lam[sl][M::geo_row(r)]; }
+        for (int r = 0; r < M::NGEO; ++r) { rho[r] = sig[M::geo_row(r)]; kappa[r] = -LAM(sl, k, M::geo_row(r)); }
         StageDer<M, T> sd;
         stage_derivatives<M, T>(zk, p, rho, kappa, exact, sd);
         f += sd.f;
@@ -284,14 +309,14 @@ struct Ipm {
         for (int i = 0; i < NV; ++i) { q1[i] = T(0); glv[i] = sd.g[i]; }
         RMPC_UNROLL
         for (int r = 0; r < M::NGEO; ++r) {
-          const T a1 = y1[M::geo_row(r)], al = lam[sl][M::geo_row(r)];
+          const T a1 = y1[M::geo_row(r)], al = LAM(sl, k, M::geo_row(r));
           RMPC_UNROLL
           for (int i = 0; i < NQ; ++i) { q1[i] -= sd.Gg[r][i] * a1; glv[i] -= sd.Gg[r][i] * al; }
         }
         RMPC_UNROLL
         for (int r = 0; r < M::NLIM; ++r) {
           q1[M::lim_var(r)] -= T(M::lim_sign(r)) * y1[M::lim_row(r)];
-          glv[M::lim_var(r)] -= T(M::lim_sign(r)) * lam[sl][M::lim_row(r)];
+          glv[M::lim_var(r)] -= T(M::lim_sign(r)) * LAM(sl, k, M::lim_row(r));
           sd.Hd[M::lim_var(r)] += sig[M::lim_row(r)];
         }
         constexpr int NQD = Dims<M>::NQD;
@@ -609,7 +634,7 @@ struct Ipm {
   // Does a row of the loaded initial guess start below delta?  (the one place a problem is classified on the GPU path)
   RMPC_HD bool starts_shifted() {
     bool shifted = false;
-    RMPC_UNROLL
+    RMPC_UNROLL_SL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
       if (k < N) {
@@ -631,12 +656,12 @@ struct Ipm {
     T mu = T(opt.mu0);
     bool pole0 = false, shifted = false;
     if constexpr (MODE != kFeasible) {  // lanes without a stage take part in the "any shift left?" votes: they must hold zeros, not what the last problem left
-      RMPC_UNROLL
+      RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl)
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) sh[sl][r] = 0.0f;
     }
-    RMPC_UNROLL
+    RMPC_UNROLL_SL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
       if (k < N) {
@@ -657,8 +682,8 @@ struct Ipm {
             sh[sl][r] = shift;
             shifted = shifted || shift > 0.0f;
           }
-          s[sl][r] = hv + T(shift);
-          lam[sl][r] = mu * trcp(hv + T(shift));
+          SLK(sl, k, r) = hv + T(shift);
+          LAM(sl, k, r) = mu * trcp(hv + T(shift));
         }
       }
     }
@@ -696,7 +721,7 @@ struct Ipm {
     load_guess(xinit, z_in);
     T mu = T(opt.mu0);
     bool pole0 = false;
-    RMPC_UNROLL
+    RMPC_UNROLL_SL
     for (int sl = 0; sl < SLOTS; ++sl) {
       const int k = g.lane + G * sl;
       if (k < N) {
@@ -707,8 +732,8 @@ struct Ipm {
         pole0 = pole0 || sv.pole;
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
-          s[sl][r] = sv.h[r];
-          lam[sl][r] = mu * trcp(sv.h[r]);
+          SLK(sl, k, r) = sv.h[r];
+          LAM(sl, k, r) = mu * trcp(sv.h[r]);
           pole0 = pole0 || !(sv.h[r] > T(0));   // float32 rounding of a row the classification (float64) found >= delta: leave it to float64
         }
       }
@@ -723,12 +748,12 @@ struct Ipm {
     const bool go_on = info.exitflag >= 0;
     if (go_on) {
       for (int e = g.lane; e < N * NV; e += G) hz[e] = float(S.st[e / NV].z[e % NV]);
-      RMPC_UNROLL
+      RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
         if (k < N) {
           RMPC_UNROLL
-          for (int r = 0; r < NH; ++r) hlam[k * NH + r] = float(lam[sl][r]);
+          for (int r = 0; r < NH; ++r) hlam[k * NH + r] = float(LAM(sl, k, r));
         }
       }
     }
@@ -753,7 +778,7 @@ struct Ipm {
       }
       const T mu = resume ? T(hmu) : T(opt.mu0);
       bool pole0 = false;
-      RMPC_UNROLL
+      RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
         if (k < N) {
@@ -768,11 +793,11 @@ struct Ipm {
               const T lr = tmax(T(hlam[k * NH + r]), T(1e-30));
               // the slack is the row's own value; where float32 rounding of z has eaten a tiny slack, a tenth of the centred
               // value mu / lambda stands in until the first accepted step re-evaluates the row
-              s[sl][r] = tmax(sv.h[r], T(0.1) * mu * trcp(lr));
-              lam[sl][r] = lr;
+              SLK(sl, k, r) = tmax(sv.h[r], T(0.1) * mu * trcp(lr));
+              LAM(sl, k, r) = lr;
             } else {
-              s[sl][r] = sv.h[r];
-              lam[sl][r] = mu * trcp(sv.h[r]);
+              SLK(sl, k, r) = sv.h[r];
+              LAM(sl, k, r) = mu * trcp(sv.h[r]);
             }
           }
         }
@@ -798,7 +823,7 @@ struct Ipm {
     for (; it <= opt.max_iter; ++it) {
       if constexpr (SH) {
         bool left = false;
-        RMPC_UNROLL
+        RMPC_UNROLL_SL
         for (int sl = 0; sl < SLOTS; ++sl)
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) left = left || sh[sl][r] > 0.0f;
@@ -853,7 +878,7 @@ struct Ipm {
       const T mu_est = mu;
       float rp = 0.0f, rpl = 0.0f, rd = 0.0f;  // step-length caps: single precision is enough (the true rows are checked in the line search)
       T dphi = T(0);
-      RMPC_UNROLL
+      RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
         if (k < N) {
@@ -863,7 +888,7 @@ struct Ipm {
           for (int c = 0; c < RV; ++c) dphi += S.st[k].g0(c) * S.st[k].dz[DS::full(c)];
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
-            const T sr = s[sl][r], lr = lam[sl][r];
+            const T sr = SLK(sl, k, r), lr = LAM(sl, k, r);
             const T shr = SH ? T(sh[sl][r]) : T(0);
             const T dsr = gd[r] - shr;                   // the step is asked to remove the whole shift
             const T rs = trcp(sr);
@@ -901,7 +926,7 @@ struct Ipm {
         T f = T(0), theta = T(0);
         LogAcc<T> la;
         bool bad = false;
-        RMPC_UNROLL
+        RMPC_UNROLL_SL
         for (int sl = 0; sl < SLOTS; ++sl) {
           const int k = g.lane + G * sl;
           if (k < N) {
@@ -922,10 +947,10 @@ struct Ipm {
                 if (shn >= 1e-12f) { stv += T(shn); theta += T(shn); }
               }
               S.st[k].Qs[r] = sv.h[r];  // kept for the update of s once the trial is accepted (K and kff are dead by now)
-              if (!(stv >= (T(1) - tau) * s[sl][r])) {
+              if (!(stv >= (T(1) - tau) * SLK(sl, k, r))) {
                 bad = true;
 #if defined(RMPC_TRACE) && !defined(__CUDA_ARCH__)
-                if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, k, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(s[sl][r]), double(lam[sl][r]), double(stv), double(s[sl][r] + alpha * gd[r]), double(alpha)); }
+                if (RMPC_TRACE > 2) { T gd[NH]; row_dirs(sl, k, gd); printf("      bad row k %d r %d s %.3g lam %.3g st %.3g lin %.3g alpha %.3g\n", k, r, double(SLK(sl, k, r)), double(LAM(sl, k, r)), double(stv), double(SLK(sl, k, r) + alpha * gd[r]), double(alpha)); }
 #endif
               }
               la.mul(tmax(stv, T(0)));
@@ -971,13 +996,13 @@ struct Ipm {
       g.sync();  // every lane has read its neighbour's z for this line search
       const T adu = tmin(ad, T(1));
       const T ikappa = T(1.0 / opt.kappa);
-      RMPC_UNROLL
+      RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
         if (k < N) {
           if (mu != mu_est) {  // the creep guard raised mu after the multiplier steps were formed: d(lambda) is linear in mu
             RMPC_UNROLL
-            for (int r = 0; r < NH; ++r) S.st[k].Qs[NH + r] += (mu - mu_est) * trcp(s[sl][r]);
+            for (int r = 0; r < NH; ++r) S.st[k].Qs[NH + r] += (mu - mu_est) * trcp(SLK(sl, k, r));
           }
           T snv[NH];  // new slacks: the row values of the accepted trial ...
           RMPC_UNROLL
@@ -993,14 +1018,14 @@ struct Ipm {
           }
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
-            const T lr = lam[sl][r];
+            const T lr = LAM(sl, k, r);
             const T dlr = S.st[k].Qs[NH + r];
             const T sn = snv[r];
             T ln = lr + adu * dlr;
             const T mus = mu * trcp(sn);
             ln = tmin(tmax(ln, mus * ikappa), T(1e10) * mus);
-            s[sl][r] = sn;
-            lam[sl][r] = ln;
+            SLK(sl, k, r) = sn;
+            LAM(sl, k, r) = ln;
           }
           RMPC_UNROLL
           for (int i = 0; i < NV; ++i) S.st[k].z[i] += alpha * S.st[k].dz[i];

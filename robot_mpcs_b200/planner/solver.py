@@ -48,9 +48,11 @@ class SolverError(RuntimeError):
     pass
 
 
-def load_library(solver_dir: str) -> ctypes.CDLL:
+def load_library(solver_dir: str, lib_dir: Optional[str] = None) -> ctypes.CDLL:
     name = os.path.basename(os.path.normpath(solver_dir))
-    path = os.path.join(solver_dir, f"lib{name}.so")
+    path = os.path.join(lib_dir or solver_dir, f"lib{name}.so")
+    if lib_dir and not os.path.isfile(path):
+        path = os.path.join(solver_dir, f"lib{name}.so")
     if not os.path.isfile(path):
         raise SolverError(f"{path} not found: generate the solver first (MpcModel.generateSolver); there is no CPU fallback")
     lib = ctypes.CDLL(path)
@@ -84,9 +86,9 @@ def load_library(solver_dir: str) -> ctypes.CDLL:
 
 
 class Solver:
-    def __init__(self, solver_dir: str, device: int = 0, max_batch: int = 1):
+    def __init__(self, solver_dir: str, device: int = 0, max_batch: int = 1, lib_dir: Optional[str] = None):
         self.dir = solver_dir
-        self.lib = load_library(solver_dir)
+        self.lib = load_library(solver_dir, lib_dir)
         d = RmpcDims()
         self.lib.rmpc_get_dims(ctypes.byref(d))
         self.N, self.nx, self.nu, self.nvar, self.npar, self.nh, self.dt = d.N, d.nx, d.nu, d.nvar, d.npar, d.nh, d.dt
@@ -99,8 +101,8 @@ class Solver:
 
     # -- reference-shaped constructor (mpcPlanner.py:73)
     @classmethod
-    def from_directory(cls, solver_dir: str, device: int = 0, max_batch: int = 1) -> "Solver":
-        return cls(solver_dir, device=device, max_batch=max_batch)
+    def from_directory(cls, solver_dir: str, device: int = 0, max_batch: int = 1, lib_dir: Optional[str] = None) -> "Solver":
+        return cls(solver_dir, device=device, max_batch=max_batch, lib_dir=lib_dir)
 
     def _err(self) -> str:
         return self.lib.rmpc_last_error().decode()
