@@ -284,8 +284,10 @@ class Bench:
     def solver(self, workload, B):
         from robot_mpcs_b200.planner.solver import Solver
         a = self.args
+        precision = getattr(self, "precision_override", None)
+        precision = a.precision if precision is None else precision
         s = Solver.from_directory(os.path.join(SOLVERS, WORKLOADS[workload][0]), device=self.local_rank, max_batch=B, lib_dir=LIB_DIR)
-        s.set_options(precision=a.precision, hessian=a.hessian, stall_window=a.stall_window)
+        s.set_options(precision=precision, hessian=a.hessian, stall_window=a.stall_window)
         return s
 
     def peaks(self):
@@ -348,6 +350,7 @@ class Bench:
 
     def measure(self, workload, B, steps, warmup, nstreams, e2e=True, latency_samples=0, cpu_sample=0, alone=True):
         torch, dist, dev, world, rank, a = self.torch, self.dist, self.dev, self.world, self.rank, self.args
+        t_begin = time.perf_counter()
         sdir, _, _, f_iter, invariant, desc = WORKLOADS[workload]
         solver = self.solver(workload, B)
         set_bytes = 8 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar)
@@ -463,6 +466,8 @@ class Bench:
             rec["cpu_baseline"], _, _ = cpu_baseline(workload, min(B, cpu_sample), seed=0)
         del sets, hosts, solver
         torch.cuda.empty_cache()
+        rec["bench_wall_s"] = time.perf_counter() - t_begin   # everything this record cost, input generation and CPU legs included
+        print(f"[bench] {workload} B={B} precision={getattr(self, 'precision_override', None)}: {rec['bench_wall_s']:.1f} s", file=sys.stderr, flush=True)
         return rec
 
     def point_robot_example(self):
@@ -509,7 +514,18 @@ def run_ours(args):
             r = b.measure("pointRobot_sweep", per, 3 if Bt >= 100000 else 10, 3, nstreams, e2e=False, latency_samples=0, cpu_sample=0, alone=False)
             sweep.append({kk: r[kk] for kk in ("value", "batch_per_gpu", "global_batch", "ms_per_step", "converged_fraction", "mean_iters", "steps")}
                          | ({"roofline_frac": r["roofline"]["frac"]} if "roofline" in r else {}))
+        # north_star's "fp32 plus fp64": the same workloads with rmpc_options.precision = 1 (float32 iterations while the barrier
+        # parameter is large, float64 to the same tolerances); the headline and every other number stay float64
+        mixed = {}
+        if args.precision == 0:
+            b.precision_override = 1
+            for w in ("pointRobot_sweep", "boxer_radial"):
+                r = b.measure(w, WORKLOADS[w][2], k, 3, nstreams, e2e=False, latency_samples=0, cpu_sample=0, alone=False)
+                mixed[w] = {kk: r[kk] for kk in ("value", "ms_per_step", "converged_fraction", "mean_iters", "steps", "gpu_launches")} | {"dtype": "f32+f64"}
+            b.precision_override = None
         if rank == 0:
+            for w, r in mixed.items():
+                (subs[w] if w in subs else rec).setdefault("precision_1", r)
             subs["pointRobot_sweep"]["batch_sweep"] = sweep
             if world == 1:
                 subs["pointRobot_example"] = b.point_robot_example()
@@ -523,7 +539,7 @@ def run_ours(args):
                         "note": "value needs several batches in flight (streams); roofline.one_batch_alone is what a closed loop, whose next step depends on this one, gets"},
                 "converged_fraction": rec["converged_fraction"], "mean_iters": rec["mean_iters"], "wall_s": rec["wall_s"], "gpu_launches": rec["gpu_launches"],
                 "roofline": rec["roofline"], "e2e": rec["e2e"], "clocks": rec["clocks"]}
-        for k in ("cpu_baseline", "single_solve_latency"):
+        for k in ("cpu_baseline", "single_solve_latency", "precision_1"):
             if k in rec:
                 line[k] = rec[k]
         if subs:

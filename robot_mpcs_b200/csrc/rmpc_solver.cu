@@ -479,15 +479,18 @@ static SolveArgs make_args(const rmpc_solver* s, const double* xinit, const doub
 // list is worked through twice on the caller's stream, in float32 (lowp_kernel) and then in float64 (solve_kernel<kResume>).
 static int launch_solve_mixed(rmpc_solver* s, int B, SolveArgs a, cudaStream_t st) {
   static_assert(kWarps == 1, "the mixed-precision kernels are one-warp blocks");
+  if (!s->slot[kSlots - 1].hit) {   // first mixed-precision call on this handle: the hand-over buffers of every slot at once
+    const size_t mb = (size_t)s->max_batch;   // (an allocation waits for the device; it must not happen between the batches of a running loop)
+    for (int i = 0; i < kSlots; ++i) {
+      Slot& a_ = s->slot[i];
+      if (!a_.hz) CK(cudaMalloc(&a_.hz, sizeof(float) * mb * M::N * M::NVAR));
+      if (!a_.hlam) CK(cudaMalloc(&a_.hlam, sizeof(float) * mb * M::N * M::NH));
+      if (!a_.hmu) CK(cudaMalloc(&a_.hmu, sizeof(float) * mb));
+      if (!a_.hit) CK(cudaMalloc(&a_.hit, sizeof(int) * mb));
+    }
+  }
   Slot& sl = s->slot[s->next_slot];
   s->next_slot = (s->next_slot + 1) % kSlots;
-  if (!sl.hz) {   // first mixed-precision call on this slot
-    const size_t mb = (size_t)s->max_batch;
-    CK(cudaMalloc(&sl.hz, sizeof(float) * mb * M::N * M::NVAR));
-    CK(cudaMalloc(&sl.hlam, sizeof(float) * mb * M::N * M::NH));
-    CK(cudaMalloc(&sl.hmu, sizeof(float) * mb));
-    CK(cudaMalloc(&sl.hit, sizeof(int) * mb));
-  }
   if (sl.used) CK(cudaStreamWaitEvent(st, sl.ev_done, 0));
   sl.used = true;
   a.ho = Handoff{sl.hz, sl.hlam, sl.hmu, sl.hit};
