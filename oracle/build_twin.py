@@ -48,7 +48,8 @@ class Twin:
         res = np.zeros((B, 6))
         o = None
         if opts is not None:
-            o = np.ascontiguousarray(opts, dtype=np.float64)
+            o = np.zeros(32)                       # trailing entries the caller did not give: 0
+            o[: len(opts)] = np.asarray(opts, dtype=np.float64)
         self.lib.twin_solve_batch(B, self._p(xinit), self._p(x0), self._p(params), self._p(z), self._p(ef), self._p(it),
                                   self._p(res), self._p(o) if o is not None else None, nthreads, precision)
         return {"z": z, "exitflag": ef, "iters": it, "obj": res[:, 0], "res_stat": res[:, 1], "res_eq": res[:, 2],

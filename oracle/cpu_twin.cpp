@@ -69,7 +69,7 @@ int twin_solve_batch(int B, const double* xinit, const double* x0, const double*
   rmpc::Options o = rmpc::default_options();
   if (opts) {
     o.max_iter = int(opts[0]); o.hessian = int(opts[1]); o.tol_stat = opts[2]; o.tol_eq = opts[3]; o.tol_ineq = opts[4];
-    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8]; o.delta = opts[9]; o.kappa = opts[10]; o.tau_min = opts[11]; o.lm0 = opts[12]; o.lm_up = opts[13]; o.lm_down = opts[14]; o.lm_trigger = opts[15]; o.creep_trigger = opts[16]; o.creep_factor = opts[17]; o.stall_window = opts[18]; o.gn_hold_max = opts[19]; o.ls_optimistic = opts[20];
+    o.tol_comp = opts[5]; o.mu0 = opts[6]; o.mu_min = opts[7]; o.reg = opts[8]; o.delta = opts[9]; o.kappa = opts[10]; o.tau_min = opts[11]; o.lm0 = opts[12]; o.lm_up = opts[13]; o.lm_down = opts[14]; o.lm_trigger = opts[15]; o.creep_trigger = opts[16]; o.creep_factor = opts[17]; o.stall_window = opts[18]; o.gn_hold_max = opts[19]; o.ls_optimistic = opts[20]; o.soc = opts[21];
   }
   if (nthreads > 0) omp_set_num_threads(nthreads);
   if (precision == 2) run<float>(B, xinit, x0, params, z_out, exitflag, iters, resid, o, false);
