@@ -44,6 +44,7 @@ WORKLOADS = {
                           "boxer N=40, 8 stage-varying half-planes (BASELINE configs[3])"),
 }
 SUB_WORKLOADS = ["pointRobot_sweep", "panda", "boxer_supermarket"]   # measured next to the headline, time-boxed
+ROLLOUTS = ["rollout_boxer_fsd", "rollout_pointRobot"]                    # device-resident closed loops
 SWEEP_B = [1000, 10000, 100000, 1000000]                             # BASELINE configs[4]: 10^3 .. 10^6 scenarios (whole job)
 
 _OUT = None
@@ -88,7 +89,7 @@ def workload_config(args, workload, B, world):
     return {"workload": f"{workload}: {WORKLOADS[workload][5]}", "batch_per_gpu": B, "global_batch": B * world, "params": args.params,
             "hessian": "exact+GN fallback" if args.hessian else "gauss-newton", "stall_window": args.stall_window,
             "tolerances": {"tol_stat": 1e-6, "tol_eq": 1e-8, "tol_ineq": 1e-8, "tol_comp": 1e-8}, "max_iter": 200,
-            "parallelism": f"scenario-sharded x{world}, all_gather of action/exitflag/iters per step"}
+            "parallelism": f"scenario-sharded x{world}, every rank's action/exitflag/iters delivered to every rank per step"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -300,9 +301,17 @@ class Bench:
         """`steps` batched solves, step i on stream i % nstreams (consecutive batches overlap: the stragglers of one batch do
         not idle the GPU); device time from the first launch to the last completion, max over ranks."""
         torch, dist, dev, world = self.torch, self.dist, self.dev, self.world
-        from robot_mpcs_b200.parallel import gather_results
+        from robot_mpcs_b200.parallel import PeerExchange, gather_results
         streams = [torch.cuda.Stream(dev) for _ in range(nstreams)]
         nsets = len(sets)
+        xchg = None
+        if world > 1 and self.args.exchange == "peer":
+            try:   # every rank's results on every rank through the library's own kernels over peer memory; all ranks or none
+                xchg = PeerExchange(solver, B, depth=8)
+            except RuntimeError as e:
+                if self.rank == 0:
+                    print("bench: peer exchange unavailable (%s): NCCL all_gather instead" % e, file=sys.stderr)
+        self.exchange_used = "none" if world == 1 else ("peer memory (rmpc_exchange_*)" if xchg else "nccl all_gather")
 
         def run(n):
             main = torch.cuda.current_stream(dev)
@@ -316,7 +325,10 @@ class Bench:
                     d = sets[i % nsets]
                     r = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
                     # the gather runs on NCCL's stream behind this step's solve; the step's stream is not held until every rank arrives
-                    gathers.append(gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True) if world > 1 else None)
+                    if xchg is not None:
+                        gathers.append(xchg.collect(xchg.publish(r["action"], r["exitflag"], r["iters"]), B * world))
+                    else:
+                        gathers.append(gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True) if world > 1 else None)
                     res.append(r)
             for st in streams:
                 ev = torch.cuda.Event()
@@ -345,6 +357,11 @@ class Bench:
         if world > 1:
             dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
             dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        if xchg is not None:
+            status = xchg.status()
+            xchg.close()
+            if status != 0:
+                raise SystemExit("bench: the peer exchange timed out (status %d)" % status)
         return {"total_s": float(total_ms) * 1e-3, "conv": float(cnt[0]), "iters": float(cnt[1]), "solved": float(cnt[2]), "rank_iters": float(iters),
                 "launches": int(launches), "wall_s": t_wall, "clock_marks": (m0, m1)}
 
@@ -494,9 +511,78 @@ class Bench:
         return rec
 
 
+def rollout_record(workload, B, T, device=0):
+    """Closed-loop rollout (the headless stand-in for examples/*_example.py): B scenarios, T control steps each =
+    measured state -> [per-step free-space decomposition] -> warm-started batched solve (`previous_plan`) -> plant step -> goal
+    check, everything on the device.  One batch at a time (the next control step depends on this one), so this is the lone-batch
+    regime.  Returns control steps/s (scenario-steps) and scenarios reached/s."""
+    import torch
+    from robot_mpcs_b200.planner.mpcPlanner import MPCPlanner
+    from robot_mpcs_b200.rollout import closed_loop
+    from robot_mpcs_b200.utils.utils import parse_setup
+    dev = torch.device("cuda", device)
+    S = SOLVERS + os.sep
+    C = os.path.join(ROOT, "robot_mpcs_b200", "config")
+
+    def corridor(seed=0):   # a corridor of lidar returns around the line from start to goal (tests/test_gpu_features.py::_corridor_scene)
+        g = np.random.default_rng(seed)
+        th = g.uniform(-np.pi, np.pi, B); xy = g.uniform(-1, 1, (B, 2)); L = g.uniform(4, 6, B)
+        dirv = np.stack([np.cos(th), np.sin(th)], 1); nrm = np.stack([-np.sin(th), np.cos(th)], 1)
+        goal = xy + L[:, None] * dirv
+        along = np.linspace(-1.5, 7.5, 32)
+        pts = np.concatenate([xy[:, None, :] + along[None, :, None] * dirv[:, None, :] + sgn * 1.6 * nrm[:, None, :] for sgn in (1.0, -1.0)], 1)
+        pts = np.concatenate([pts, np.full((B, 64, 1), 0.02)], 2)
+        xinit = np.concatenate([xy, (th + g.uniform(-0.4, 0.4, B))[:, None], np.zeros((B, 3)), g.uniform(0, 0.3, (B, 1)), np.zeros((B, 1))], 1)
+        return xinit, goal, np.ascontiguousarray(pts)
+
+    def scene():
+        if workload == "rollout_pointRobot":
+            setup = parse_setup(os.path.join(C, "pointRobotMpc.yaml"))["mpc"]; setup["initialization"] = "previous_plan"
+            pl = MPCPlanner("pointRobot", S, batch_size=B, device_resident=True, **setup); pl.concretize(); pl.reset()
+            pm = load_paramMap("pointRobot_n3_005_H20_noSlack")
+            s = sc.point_robot_sweep(pm, B, seed=5)
+            pl._params3[:] = torch.as_tensor(s["params"], device=dev)
+            return pl, torch.as_tensor(s["xinit"], device=dev), torch.as_tensor(s["params"][:, 0, pm["goal"]], device=dev), dict(epsilon=0.2)
+        setup = parse_setup(os.path.join(C, "boxerSupermarketMpc.yaml"))["mpc"]; setup["initialization"] = "previous_plan"
+        xinit, goal, pts = corridor()
+        pl = MPCPlanner("boxer", S, batch_size=B, device_resident=True, **setup); pl.concretize(); pl.reset()
+        pl.setLinearConstraints(np.tile([1.0, 0.0, 0.0, 100.0], (setup["time_horizon"], setup["number_obstacles"], 1)), 0.6)
+        pl.setJointLimits(np.array([[-30.0] * 3, [30.0] * 3])); pl.setInputLimits(np.array([[-10.0] * 2, [10.0] * 2]))
+        g = torch.as_tensor(goal, device=dev); pl.setGoalReaching(g); pl.setConstraintAvoidance()
+        return pl, torch.as_tensor(xinit, device=dev), g, dict(epsilon=0.4, fsd_points=torch.as_tensor(pts, device=dev))
+
+    with torch.cuda.device(dev):
+        pl, x0, goal, kw = scene()
+        closed_loop(pl, x0, goal, 3, **kw)                      # warm-up (allocations, first launches)
+        pl, x0, goal, kw = scene()
+        torch.cuda.synchronize()
+        l0 = pl._solver.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t = time.perf_counter(); e0.record()
+        r = closed_loop(pl, x0, goal, T, **kw)
+        e1.record(); torch.cuda.synchronize(); wall = time.perf_counter() - t
+    dev_s = e0.elapsed_time(e1) * 1e-3
+    reached = int(r["reached"].sum())
+    per_step = ("free-space decomposition (N x K=8 planes from 64 lidar returns) + solve (boxer N=40) + plant step + goal check"
+                if workload == "rollout_boxer_fsd" else "solve (pointRobot N=20) + plant step + goal check")
+    return {"metric": "closed-loop control steps/s (scenario-steps)", "value": B * T / dev_s, "unit": "control steps/s",
+            "scenarios_reached_per_s": reached / dev_s, "reached_fraction": reached / B, "ms_per_control_step": 1e3 * dev_s / T, "wall_s": wall,
+            "config": {"workload": workload, "batch": B, "control_steps": T, "initialization": "previous_plan", "per_step": per_step},
+            "mean_iters_first_step": float(r["mean_iters"][0]), "mean_iters_warm": float(r["mean_iters"][5:].mean()),
+            "failed_solves": int(r["failures"].sum()), "gpu_launches": int(pl._solver.launch_count() - l0), "dtype": "f64", "data": "synthetic"}
+
+
 def run_ours(args):
     b = Bench(args)
     rank, world = b.rank, b.world
+    if args.workload in ROLLOUTS:   # closed-loop workloads: their own record is the line (rank 0's GPU; a rollout shards like any batch)
+        if rank == 0:
+            rec = rollout_record(args.workload, args.batch or 4096, args.steps, b.local_rank)
+            b.sampler.stop()
+            emit(rec | {"n_gpus": 1, "steps": args.steps, "warmup": 3, "higher_is_better": True, "clocks": b.sampler.summary()})
+        if world > 1:
+            b.dist.destroy_process_group()
+        return
     defB = WORKLOADS[args.workload][2]
     B = args.batch or defB
     nstreams = max(1, args.streams)
@@ -529,13 +615,15 @@ def run_ours(args):
             subs["pointRobot_sweep"]["batch_sweep"] = sweep
             if world == 1:
                 subs["pointRobot_example"] = b.point_robot_example()
+                for w in ROLLOUTS:   # control steps/s and scenarios reached/s with previous_plan warm starts
+                    subs[w] = rollout_record(w, 4096, 40 if w == "rollout_boxer_fsd" else 160, b.local_rank)
     if rank == 0:
         b.sampler.stop()
         line = {"metric": "converged MPC solves/sec", "value": rec["value"], "unit": "converged solves/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": {0: "f64", 1: "f32+f64"}[args.precision], "data": "synthetic",
                 "config": workload_config(args, args.workload, B, world),
-                "run": {"streams": nstreams, "l2": rec["l2"] + "; single-batch timing with L2 flushed (256 MB write)",
+                "run": {"streams": nstreams, "exchange": getattr(b, "exchange_used", "none"), "l2": rec["l2"] + "; single-batch timing with L2 flushed (256 MB write)",
                         "note": "value needs several batches in flight (streams); roofline.one_batch_alone is what a closed loop, whose next step depends on this one, gets"},
                 "converged_fraction": rec["converged_fraction"], "mean_iters": rec["mean_iters"], "wall_s": rec["wall_s"], "gpu_launches": rec["gpu_launches"],
                 "roofline": rec["roofline"], "e2e": rec["e2e"], "clocks": rec["clocks"]}
@@ -554,7 +642,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="boxer_radial", choices=list(WORKLOADS))
+    ap.add_argument("--workload", default="boxer_radial", choices=list(WORKLOADS) + ROLLOUTS)
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", type=int, default=0)
@@ -566,6 +654,9 @@ def main():
                     help="device-resident parameter format: the reference's all_parameters[N*npar] per problem, or one npar block per problem "
                          "for workloads whose parameters do not vary over the horizon (rmpc_solve_batch_strided, stage stride 0)")
     ap.add_argument("--streams", type=int, default=4, help="CUDA streams the consecutive batches are spread over (1 = strictly one batch at a time)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: how every rank gets every rank's (action, exitflag, iters) of a step: the library's kernels over peer memory "
+                         "(CUDA IPC, NVLink) or one NCCL all_gather per step")
     ap.add_argument("--stall-window", type=int, default=0, help="rmpc_options.stall_window (0 = off, the default)")
     ap.add_argument("--latency-samples", type=int, default=1000, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
     args = ap.parse_args()
@@ -577,6 +668,8 @@ def main():
     _OUT = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
     if args.impl == "reference":
+        if args.workload in ROLLOUTS:
+            raise SystemExit("--impl reference times the batched solve; the closed-loop workloads have no CPU arm")
         run_reference(args)
     else:
         run_ours(args)

@@ -30,6 +30,8 @@
 #ifndef RMPC_H
 #define RMPC_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -155,6 +157,41 @@ int rmpc_predict_obstacles(rmpc_solver* s, int B, const double* obst_state, int 
 int rmpc_solve_batch_static(int B, const double* xinit, const double* x0, const double* params, double* z_out,
                             double* action_out, const rmpc_info* info, const rmpc_options* opt, void* stream);
 int rmpc_static_max_batch(void);
+
+/* ---- Result exchange between the ranks of one node over peer memory (NVLink / NVSwitch) --------------------------------
+ * No counterpart in the reference (a single process, one solve at a time).  The scenario batch is sharded over one process
+ * per GPU and the solve needs no collective; these calls hand every rank the whole batch's (action, exitflag, iterations)
+ * of a step without NCCL: each rank owns one device region which its peers map through CUDA IPC, a small kernel behind the
+ * rank's solve stores its rows into every rank's region (posted peer stores) and raises one flag per (step, rank), and the
+ * collecting side waits for the world's flags with ONE resident warp, unpacks, and acknowledges the ring slot
+ * (csrc/rmpc_exchange.cuh states the protocol and why it cannot deadlock).  Rules:
+ *   - publish is called in the same order on every rank (it numbers the steps), collect in step order after its publish;
+ *   - at most `depth` steps may be published ahead of the slowest rank's collects: a publish beyond that waits on the device;
+ *   - a wait that lasts longer than 20 s gives up and raises the status word (rmpc_exchange_status != 0) instead of
+ *     hanging the GPU; results after that are undefined;
+ *   - rows_per_rank >= every rank's shard; row i of the collected arrays is row i % rows_per_rank of rank i / rows_per_rank.
+ * rmpc_ipc_alloc returns zeroed device memory and its 64-byte cudaIpcMemHandle_t, rmpc_ipc_open maps a peer's handle into
+ * this process (same node, peer access enabled lazily); regions[w] of rmpc_exchange_create is rank w's region as seen from
+ * this process (regions[rank] is the rank's own allocation).  Inside one process the regions can be passed around as plain
+ * pointers, which is how tests/test_gpu_exchange.py runs two ranks on one GPU. */
+typedef struct rmpc_exchange rmpc_exchange;
+size_t rmpc_exchange_region_bytes(int world, int rows_per_rank, int depth);   /* 0 = bad argument */
+int rmpc_ipc_alloc(int device, size_t bytes, void** ptr, unsigned char* handle64 /* may be NULL */);
+int rmpc_ipc_open(int device, const unsigned char* handle64, void** ptr);
+int rmpc_ipc_close(int device, void* ptr);
+int rmpc_ipc_free(int device, void* ptr);
+rmpc_exchange* rmpc_exchange_create(int device, int world, int rank, int rows_per_rank, int depth, void* const* regions);
+void rmpc_exchange_destroy(rmpc_exchange* x);
+/* Enqueues on `stream` (behind the solve that produced them) the stores of this rank's B rows action[B][nu], exitflag[B],
+ * iters[B] (device pointers; exitflag / iters may be NULL) into every rank's region.  Returns the step number, -1 on error. */
+long rmpc_exchange_publish(rmpc_exchange* x, int B, const double* action, const int* exitflag, const int* iters, void* stream);
+/* Step `seq` of every rank into action_all[world * rows_per_rank][nu], exitflag_all[...], iters_all[...] (device pointers, the
+ * int arrays may be NULL).  The wait for the slowest rank and the unpack run on the exchange's own stream, the unpack behind
+ * everything `stream` holds at the time of the call (so the output arrays may be fresh from a stream-ordered allocator);
+ * `stream` itself is not held.  rmpc_exchange_join makes `stream` wait for every collect enqueued so far. */
+int rmpc_exchange_collect(rmpc_exchange* x, long seq, double* action_all, int* exitflag_all, int* iters_all, void* stream);
+int rmpc_exchange_join(rmpc_exchange* x, void* stream);
+int rmpc_exchange_status(rmpc_exchange* x);   /* 0 ok, 1 a publish timed out waiting for a slot, 2 a collect timed out; synchronises */
 
 /* Number of CUDA kernels this library has launched since it was loaded (bench.py reports it). */
 long rmpc_launch_count(void);

@@ -20,6 +20,7 @@
 #define RMPC_WARPS RMPC_WARPS_FIXED
 #include "rmpc_ipm.cuh"
 #include "rmpc_fsd.cuh"
+#include "rmpc_exchange.cuh"
 #include "rmpc.h"
 
 using M = ModelTraits;
@@ -918,6 +919,150 @@ int rmpc_solve_batch_static(int B, const double* xinit, const double* x0, const 
   g_launches++;
   CK(cudaGetLastError());
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Result exchange over peer memory (rmpc_exchange.cuh): host side.
+struct rmpc_exchange {
+  int device;
+  rmpc_x::View view;
+  std::mutex mu;
+  long next_publish, next_collect;
+  cudaStream_t xstream;   // the collects of this rank, in step order
+  cudaEvent_t ev;
+};
+
+size_t rmpc_exchange_region_bytes(int world, int rows_per_rank, int depth) {
+  if (world < 1 || world > rmpc_x::kMaxWorld || rows_per_rank < 1 || depth < 1) return 0;
+  return rmpc_x::Layout{world, rows_per_rank, M::NU + 1, depth}.bytes();
+}
+
+int rmpc_ipc_alloc(int device, size_t bytes, void** ptr, unsigned char* handle64) {
+  if (!ptr || bytes == 0) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  DeviceGuard guard(device); CK(guard.err);
+  CK(cudaMalloc(ptr, bytes));
+  CK(cudaMemset(*ptr, 0, bytes));
+  CK(cudaDeviceSynchronize());
+  if (handle64) {
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, *ptr));
+    memcpy(handle64, &h, 64);
+  }
+  return 0;
+}
+
+int rmpc_ipc_open(int device, const unsigned char* handle64, void** ptr) {
+  if (!ptr || !handle64) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  DeviceGuard guard(device); CK(guard.err);
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  CK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+int rmpc_ipc_close(int device, void* ptr) {
+  DeviceGuard guard(device); CK(guard.err);
+  CK(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+
+int rmpc_ipc_free(int device, void* ptr) {
+  DeviceGuard guard(device); CK(guard.err);
+  CK(cudaFree(ptr));
+  return 0;
+}
+
+rmpc_exchange* rmpc_exchange_create(int device, int world, int rank, int rows_per_rank, int depth, void* const* regions) {
+  if (world < 1 || world > rmpc_x::kMaxWorld || rank < 0 || rank >= world || rows_per_rank < 1 || depth < 1 || !regions) {
+    snprintf(g_err, sizeof g_err, "rmpc_exchange_create: world 1..%d, 0 <= rank < world, rows_per_rank >= 1, depth >= 1", rmpc_x::kMaxWorld);
+    return nullptr;
+  }
+  for (int w = 0; w < world; ++w)
+    if (!regions[w]) { snprintf(g_err, sizeof g_err, "rmpc_exchange_create: region %d is NULL", w); return nullptr; }
+  DeviceGuard guard(device);
+  if (guard.err != cudaSuccess) { snprintf(g_err, sizeof g_err, "cudaSetDevice(%d): %s", device, cudaGetErrorString(guard.err)); return nullptr; }
+  auto* x = new rmpc_exchange();
+  x->device = device;
+  x->view.l = rmpc_x::Layout{world, rows_per_rank, M::NU + 1, depth};
+  x->view.rank = rank;
+  for (int w = 0; w < rmpc_x::kMaxWorld; ++w) x->view.region[w] = w < world ? static_cast<char*>(regions[w]) : nullptr;
+  x->next_publish = x->next_collect = 0;
+  if (cudaStreamCreateWithFlags(&x->xstream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&x->ev, cudaEventDisableTiming) != cudaSuccess) {
+    snprintf(g_err, sizeof g_err, "rmpc_exchange_create: %s", cudaGetErrorString(cudaGetLastError()));
+    delete x;
+    return nullptr;
+  }
+  return x;
+}
+
+void rmpc_exchange_destroy(rmpc_exchange* x) {
+  if (!x) return;
+  DeviceGuard guard(x->device);
+  cudaStreamSynchronize(x->xstream);
+  cudaStreamDestroy(x->xstream);
+  cudaEventDestroy(x->ev);
+  delete x;
+}
+
+long rmpc_exchange_publish(rmpc_exchange* x, int B, const double* action, const int* exitflag, const int* iters, void* stream) {
+  if (!x || !action || B < 0 || B > x->view.l.rows) { snprintf(g_err, sizeof g_err, "rmpc_exchange_publish: 0 <= B <= rows_per_rank (%d)", x ? x->view.l.rows : 0); return -1; }
+  std::lock_guard<std::mutex> lock(x->mu);
+  GUARD(x);
+  const long seq = x->next_publish;
+  const int depth = x->view.l.depth, slot = int(seq % depth);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (seq >= depth) {   // the slot is free once every rank has collected the step that used it last
+    rmpc_x::wait_kernel<<<1, 32, 0, st>>>(x->view, 0, 0, (unsigned long long)(seq - depth + 1));
+    g_launches++;
+  }
+  const int blocks = B > 0 ? (B + 255) / 256 : 1;
+  rmpc_x::publish_kernel<<<blocks, 256, 0, st>>>(x->view, slot, (unsigned long long)(seq + 1), B, M::NU, action, exitflag, iters);
+  g_launches++;
+  CK(cudaGetLastError());
+  x->next_publish = seq + 1;
+  return seq;
+}
+
+int rmpc_exchange_collect(rmpc_exchange* x, long seq, double* action_all, int* exitflag_all, int* iters_all, void* stream) {
+  if (!x || !action_all) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  std::lock_guard<std::mutex> lock(x->mu);
+  if (seq != x->next_collect || seq >= x->next_publish) {
+    snprintf(g_err, sizeof g_err, "rmpc_exchange_collect: steps are collected in order, after their publish (next %ld, published %ld, asked %ld)",
+             x->next_collect, x->next_publish, seq);
+    return -1;
+  }
+  GUARD(x);
+  const int slot = int(seq % x->view.l.depth);
+  const int total = x->view.l.world * x->view.l.rows;
+  // the waiting warp and the unpack run on the exchange's own stream: no solve stream is held until the slowest rank arrives.
+  // The unpack is ordered behind what `stream` holds so far (the output buffers may come from a stream-ordered allocator).
+  rmpc_x::wait_kernel<<<1, 32, 0, x->xstream>>>(x->view, 1, slot, (unsigned long long)(seq + 1));
+  CK(cudaEventRecord(x->ev, (cudaStream_t)stream));
+  CK(cudaStreamWaitEvent(x->xstream, x->ev, 0));
+  rmpc_x::unpack_kernel<<<(total + 255) / 256, 256, 0, x->xstream>>>(x->view, slot, (unsigned long long)(seq + 1), M::NU, action_all, exitflag_all, iters_all);
+  g_launches += 2;
+  CK(cudaGetLastError());
+  x->next_collect = seq + 1;
+  return 0;
+}
+
+int rmpc_exchange_join(rmpc_exchange* x, void* stream) {
+  if (!x) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  std::lock_guard<std::mutex> lock(x->mu);
+  GUARD(x);
+  CK(cudaEventRecord(x->ev, x->xstream));
+  CK(cudaStreamWaitEvent((cudaStream_t)stream, x->ev, 0));
+  return 0;
+}
+
+int rmpc_exchange_status(rmpc_exchange* x) {
+  if (!x) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  std::lock_guard<std::mutex> lock(x->mu);
+  GUARD(x);
+  unsigned long long st = 0;
+  CK(cudaMemcpy(&st, x->view.region[x->view.rank], sizeof st, cudaMemcpyDeviceToHost));   // synchronises with the device
+  return int(st);
 }
 
 int rmpc_static_max_batch(void) { return kStaticMaxBatch; }

@@ -41,7 +41,9 @@ class RmpcInfo(ctypes.Structure):
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
            "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_strided", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
-           "rmpc_set_params", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_solve_batch_static", "rmpc_static_max_batch", "rmpc_launch_count"]
+           "rmpc_set_params", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_solve_batch_static", "rmpc_static_max_batch", "rmpc_launch_count",
+           "rmpc_exchange_region_bytes", "rmpc_ipc_alloc", "rmpc_ipc_open", "rmpc_ipc_close", "rmpc_ipc_free", "rmpc_exchange_create",
+           "rmpc_exchange_destroy", "rmpc_exchange_publish", "rmpc_exchange_collect", "rmpc_exchange_join", "rmpc_exchange_status"]
 
 
 class SolverError(RuntimeError):
@@ -82,6 +84,20 @@ def load_library(solver_dir: str, lib_dir: Optional[str] = None) -> ctypes.CDLL:
                                            ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
     lib.rmpc_solve_batch_static.argtypes = ([ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo), ctypes.POINTER(RmpcOptions), ctypes.c_void_p])
     lib.rmpc_launch_count.restype = ctypes.c_long
+    lib.rmpc_exchange_region_bytes.restype = ctypes.c_size_t
+    lib.rmpc_exchange_region_bytes.argtypes = [ctypes.c_int] * 3
+    lib.rmpc_ipc_alloc.argtypes = [ctypes.c_int, ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p), ctypes.c_char_p]
+    lib.rmpc_ipc_open.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]
+    lib.rmpc_ipc_close.argtypes = [ctypes.c_int, ctypes.c_void_p]
+    lib.rmpc_ipc_free.argtypes = [ctypes.c_int, ctypes.c_void_p]
+    lib.rmpc_exchange_create.restype = ctypes.c_void_p
+    lib.rmpc_exchange_create.argtypes = [ctypes.c_int] * 5 + [ctypes.POINTER(ctypes.c_void_p)]
+    lib.rmpc_exchange_destroy.argtypes = [ctypes.c_void_p]
+    lib.rmpc_exchange_publish.restype = ctypes.c_long
+    lib.rmpc_exchange_publish.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 4
+    lib.rmpc_exchange_collect.argtypes = [ctypes.c_void_p, ctypes.c_long] + [ctypes.c_void_p] * 4
+    lib.rmpc_exchange_join.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.rmpc_exchange_status.argtypes = [ctypes.c_void_p]
     return lib
 
 
