@@ -311,7 +311,8 @@ class Bench:
             except RuntimeError as e:
                 if self.rank == 0:
                     print("bench: peer exchange unavailable (%s): NCCL all_gather instead" % e, file=sys.stderr)
-        self.exchange_used = "none" if world == 1 else ("peer memory (rmpc_exchange_*)" if xchg else "nccl all_gather")
+        no_exchange = world == 1 or self.args.exchange == "none"
+        self.exchange_used = "none" if no_exchange else ("peer memory (rmpc_exchange_*)" if xchg else "nccl all_gather")
 
         def run(n):
             main = torch.cuda.current_stream(dev)
@@ -322,13 +323,13 @@ class Bench:
             res, gathers = [], []
             for i in range(n):
                 with torch.cuda.stream(streams[i % nstreams]):
-                    d = sets[i % nsets]
+                    d = sets[(i + self.rank) % nsets]   # every rank holds the same sets (weak scaling: identical work per GPU), rotated by rank
                     r = solver.solve_batch(d["xinit"], d["x0"], d["params"], want_z=False, want_info=True)
                     # the gather runs on NCCL's stream behind this step's solve; the step's stream is not held until every rank arrives
                     if xchg is not None:
                         gathers.append(xchg.collect(xchg.publish(r["action"], r["exitflag"], r["iters"]), B * world))
                     else:
-                        gathers.append(gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True) if world > 1 else None)
+                        gathers.append(None if no_exchange else gather_results(r["action"], r["exitflag"], r["iters"], B * world, async_op=True))
                     res.append(r)
             for st in streams:
                 ev = torch.cuda.Event()
@@ -354,7 +355,11 @@ class Bench:
         iters = sum(int(r["iters"].sum()) for r in results)
         total_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         cnt = torch.tensor([conv, iters, B * len(results)], dtype=torch.float64, device=dev)
+        rank_ms = [float(total_ms) / len(results)]
         if world > 1:
+            every = torch.zeros(world, dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(every, total_ms)
+            rank_ms = [float(v) / len(results) for v in every]
             dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
             dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
         if xchg is not None:
@@ -363,7 +368,7 @@ class Bench:
             if status != 0:
                 raise SystemExit("bench: the peer exchange timed out (status %d)" % status)
         return {"total_s": float(total_ms) * 1e-3, "conv": float(cnt[0]), "iters": float(cnt[1]), "solved": float(cnt[2]), "rank_iters": float(iters),
-                "launches": int(launches), "wall_s": t_wall, "clock_marks": (m0, m1)}
+                "launches": int(launches), "wall_s": t_wall, "clock_marks": (m0, m1), "rank_ms": rank_ms}
 
     def measure(self, workload, B, steps, warmup, nstreams, e2e=True, latency_samples=0, cpu_sample=0, alone=True):
         torch, dist, dev, world, rank, a = self.torch, self.dist, self.dev, self.world, self.rank, self.args
@@ -376,12 +381,12 @@ class Bench:
         hosts, sets = [], []
         for i in range(nsets):
             if e2e:
-                s = make_inputs(workload, B, seed=1000 * rank + i)
+                s = make_inputs(workload, B, seed=i)
                 host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in s.items()}
                 hosts.append(host)
                 devt = {k: v.to(dev) for k, v in host.items()}
             else:
-                devt = make_inputs_device(torch, dev, workload, B, 1000 * rank + i, solver.N)
+                devt = make_inputs_device(torch, dev, workload, B, i, solver.N)
             if a.params == "compressed":
                 p3 = devt["params"].view(B, solver.N, solver.npar)
                 if not bool((p3 == p3[:, :1]).all()):
@@ -392,8 +397,10 @@ class Bench:
         total_s = tp["total_s"]
         rec = {"value": tp["conv"] / total_s, "unit": "converged solves/s", "batch_per_gpu": B, "global_batch": B * world, "steps": steps, "warmup": warmup,
                "ms_per_step": 1e3 * total_s / steps, "converged_fraction": tp["conv"] / tp["solved"], "mean_iters": tp["iters"] / tp["solved"],
-               "gpu_launches": tp["launches"], "wall_s": tp["wall_s"], "streams": nstreams,
-               "l2": f"{nsets} rotating input set(s) of {set_bytes / 1e6:.0f} MB (> 126 MB L2 in total)"}
+               "gpu_launches": tp["launches"], "wall_s": tp["wall_s"], "streams": nstreams, "ms_per_step_by_rank": tp["rank_ms"],
+               "l2": f"{nsets} rotating input set(s) of {set_bytes / 1e6:.0f} MB (> 126 MB L2 in total); every rank holds the same sets and starts its rotation "
+                     "at set number `rank`: per-GPU work is identical at every N (a batch lasts as long as its slowest problem, and with different "
+                     "scenarios per rank the slowest rank's draw, not the exchange, set the N-GPU time: profiles/r2x_exchange_ab.txt)"}
         bytes_alg = 8.0 * B * (solver.nx + solver.N * solver.nvar + solver.N * solver.npar) + 8.0 * B * (solver.nu + 1) + 4.0 * B * 2
         if rank == 0:
             rec["clocks"] = self.sampler.summary(*tp["clock_marks"])
@@ -450,7 +457,7 @@ class Bench:
                         conv += int((pend[j]["exitflag"] == 1).sum())
                         pend[j] = None
                     if i < n:
-                        hh = hnp[i % nsets]
+                        hh = hnp[(i + rank) % nsets]
                         pend[j] = hsolvers[j].solve_batch(hh["xinit"], hh["x0"], hh["params"], want_z=False, want_info=True, block=False)
                 return conv
 
@@ -623,7 +630,7 @@ def run_ours(args):
                 "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": {0: "f64", 1: "f32+f64"}[args.precision], "data": "synthetic",
                 "config": workload_config(args, args.workload, B, world),
-                "run": {"streams": nstreams, "exchange": getattr(b, "exchange_used", "none"), "l2": rec["l2"] + "; single-batch timing with L2 flushed (256 MB write)",
+                "run": {"streams": nstreams, "exchange": getattr(b, "exchange_used", "none"), "ms_per_step_by_rank": rec["ms_per_step_by_rank"], "l2": rec["l2"] + "; single-batch timing with L2 flushed (256 MB write)",
                         "note": "value needs several batches in flight (streams); roofline.one_batch_alone is what a closed loop, whose next step depends on this one, gets"},
                 "converged_fraction": rec["converged_fraction"], "mean_iters": rec["mean_iters"], "wall_s": rec["wall_s"], "gpu_launches": rec["gpu_launches"],
                 "roofline": rec["roofline"], "e2e": rec["e2e"], "clocks": rec["clocks"]}
@@ -654,9 +661,9 @@ def main():
                     help="device-resident parameter format: the reference's all_parameters[N*npar] per problem, or one npar block per problem "
                          "for workloads whose parameters do not vary over the horizon (rmpc_solve_batch_strided, stage stride 0)")
     ap.add_argument("--streams", type=int, default=4, help="CUDA streams the consecutive batches are spread over (1 = strictly one batch at a time)")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl", "none"],
                     help="N > 1: how every rank gets every rank's (action, exitflag, iters) of a step: the library's kernels over peer memory "
-                         "(CUDA IPC, NVLink) or one NCCL all_gather per step")
+                         "(CUDA IPC, NVLink), one NCCL all_gather per step, or nothing (results stay on their rank: the cost of either is the difference)")
     ap.add_argument("--stall-window", type=int, default=0, help="rmpc_options.stall_window (0 = off, the default)")
     ap.add_argument("--latency-samples", type=int, default=1000, help="single solves (B=1) timed for the p50/p99 latency; 0 = skip")
     args = ap.parse_args()

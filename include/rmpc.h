@@ -182,8 +182,10 @@ int rmpc_ipc_close(int device, void* ptr);
 int rmpc_ipc_free(int device, void* ptr);
 rmpc_exchange* rmpc_exchange_create(int device, int world, int rank, int rows_per_rank, int depth, void* const* regions);
 void rmpc_exchange_destroy(rmpc_exchange* x);
-/* Enqueues on `stream` (behind the solve that produced them) the stores of this rank's B rows action[B][nu], exitflag[B],
- * iters[B] (device pointers; exitflag / iters may be NULL) into every rank's region.  Returns the step number, -1 on error. */
+/* Stores this rank's B rows action[B][nu], exitflag[B], iters[B] (device pointers; exitflag / iters may be NULL) into every
+ * rank's region, on the exchange's own stream behind everything `stream` holds at the time of the call (the solve that
+ * produces them); `stream` itself is never held.  The arrays must stay valid until the step has been collected.  Returns
+ * the step number, -1 on error. */
 long rmpc_exchange_publish(rmpc_exchange* x, int B, const double* action, const int* exitflag, const int* iters, void* stream);
 /* Step `seq` of every rank into action_all[world * rows_per_rank][nu], exitflag_all[...], iters_all[...] (device pointers, the
  * int arrays may be NULL).  The wait for the slowest rank and the unpack run on the exchange's own stream, the unpack behind

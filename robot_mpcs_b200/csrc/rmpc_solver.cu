@@ -928,6 +928,7 @@ struct rmpc_exchange {
   rmpc_x::View view;
   std::mutex mu;
   long next_publish, next_collect;
+  cudaStream_t pstream;   // the publishes of this rank, in step order, each behind the solve it belongs to
   cudaStream_t xstream;   // the collects of this rank, in step order
   cudaEvent_t ev;
 };
@@ -988,7 +989,7 @@ rmpc_exchange* rmpc_exchange_create(int device, int world, int rank, int rows_pe
   x->view.rank = rank;
   for (int w = 0; w < rmpc_x::kMaxWorld; ++w) x->view.region[w] = w < world ? static_cast<char*>(regions[w]) : nullptr;
   x->next_publish = x->next_collect = 0;
-  if (cudaStreamCreateWithFlags(&x->xstream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&x->ev, cudaEventDisableTiming) != cudaSuccess) {
+  if (cudaStreamCreateWithFlags(&x->pstream, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&x->xstream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&x->ev, cudaEventDisableTiming) != cudaSuccess) {
     snprintf(g_err, sizeof g_err, "rmpc_exchange_create: %s", cudaGetErrorString(cudaGetLastError()));
     delete x;
     return nullptr;
@@ -999,7 +1000,9 @@ rmpc_exchange* rmpc_exchange_create(int device, int world, int rank, int rows_pe
 void rmpc_exchange_destroy(rmpc_exchange* x) {
   if (!x) return;
   DeviceGuard guard(x->device);
+  cudaStreamSynchronize(x->pstream);
   cudaStreamSynchronize(x->xstream);
+  cudaStreamDestroy(x->pstream);
   cudaStreamDestroy(x->xstream);
   cudaEventDestroy(x->ev);
   delete x;
@@ -1011,7 +1014,11 @@ long rmpc_exchange_publish(rmpc_exchange* x, int B, const double* action, const 
   GUARD(x);
   const long seq = x->next_publish;
   const int depth = x->view.l.depth, slot = int(seq % depth);
-  cudaStream_t st = (cudaStream_t)stream;
+  // The stores run on the exchange's own stream behind what `stream` holds now (the solve): a publish that has to wait for
+  // a free ring slot, i.e. for the slowest rank, then holds up later publishes but never a solve.
+  cudaStream_t st = x->pstream;
+  CK(cudaEventRecord(x->ev, (cudaStream_t)stream));
+  CK(cudaStreamWaitEvent(st, x->ev, 0));
   if (seq >= depth) {   // the slot is free once every rank has collected the step that used it last
     rmpc_x::wait_kernel<<<1, 32, 0, st>>>(x->view, 0, 0, (unsigned long long)(seq - depth + 1));
     g_launches++;

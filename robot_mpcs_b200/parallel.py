@@ -153,7 +153,8 @@ class PeerExchange:
         return out
 
     def publish(self, action: torch.Tensor, exitflag: torch.Tensor, iters: torch.Tensor) -> int:
-        """Enqueued on the current stream, i.e. behind the solve that wrote the three tensors.  Returns the step number."""
+        """Enqueued behind what the current stream holds now, i.e. behind the solve that writes the three tensors (keep them
+        until the step is collected).  Returns the step number."""
         assert action.is_cuda and action.dtype == torch.float64 and action.is_contiguous() and action.shape[1] == self.nu
         assert exitflag.dtype == torch.int32 and iters.dtype == torch.int32
         stream = torch.cuda.current_stream(action.device).cuda_stream

@@ -17,9 +17,12 @@ dev = torch.device("cuda", local)
 init_process_group("nccl", device_id=dev)
 sdir = os.path.join(ROOT, "robot_mpcs_b200", "solvers", "boxer_n3_01_H30_noSlack")
 pm = yaml.safe_load(open(os.path.join(sdir, "paramMap.yaml")))
-per, steps, depth = 1024, 30, 4
-B = per - (7 if rank == world - 1 else 0)            # the last shard is short
-total = per * (world - 1) + per - 7
+from robot_mpcs_b200.parallel import shard_bounds
+steps, depth = 30, 4
+total = 1024 * world - 7                              # the last shard is short
+per = -(-total // world)
+lo, hi = shard_bounds(total, rank, world)
+B = hi - lo
 solver = Solver.from_directory(sdir, device=local, max_batch=per)
 x = PeerExchange(solver, per, depth)
 streams = [torch.cuda.Stream(dev) for _ in range(3)]
