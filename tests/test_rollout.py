@@ -105,3 +105,17 @@ def test_point_robot_follows_global_path(built):
           "max dist", float(r["goal_distance"].max()), "d0 min", float(d0.min()))
     assert float(near.double().mean()) > 0.9
     assert bool((r["goal_distance"] < d0 + 1.5).all())
+
+
+@pytest.mark.parametrize("workload,T", [("rollout_boxer_fsd", 45), ("rollout_pointRobot", 12)])
+def test_bench_rollout_records(built, workload, T):
+    """bench.py's closed-loop records (control steps/s, scenarios reached/s with previous_plan warm starts)."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    r = bench.rollout_record(workload, 128, T)
+    assert r["value"] > 0 and r["failed_solves"] == 0 and r["gpu_launches"] >= 3 * T
+    assert r["config"]["initialization"] == "previous_plan" and r["config"]["control_steps"] == T
+    assert r["mean_iters_warm"] < r["mean_iters_first_step"]          # warm starts pay
+    if workload == "rollout_boxer_fsd":
+        assert r["reached_fraction"] >= 0.95 and r["scenarios_reached_per_s"] > 0
