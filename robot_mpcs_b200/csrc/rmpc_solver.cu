@@ -933,6 +933,7 @@ struct rmpc_exchange {
   cudaEvent_t ev;
 };
 
+static_assert(M::NU + 1 <= 8, "publish_kernel stages a row of at most 8 doubles");
 size_t rmpc_exchange_region_bytes(int world, int rows_per_rank, int depth) {
   if (world < 1 || world > rmpc_x::kMaxWorld || rows_per_rank < 1 || depth < 1) return 0;
   return rmpc_x::Layout{world, rows_per_rank, M::NU + 1, depth}.bytes();

@@ -43,3 +43,18 @@ def test_no_gpu_fails_loudly(built):
     from robot_mpcs_b200.planner.solver import Solver, SolverError
     with pytest.raises(SolverError, match="no CPU fallback|no usable CUDA"):
         Solver.from_directory(os.path.join(SOLVERS, "pointRobot_n3_005_H20_noSlack"), device=0, max_batch=1)
+
+
+def test_exchange_region_layout_is_host_arithmetic(built):
+    """rmpc_exchange_region_bytes needs no device: status | flags[depth][world] | acks[world] | counters[2][depth] | rows (256-byte
+    aligned) of world * depth * rows_per_rank * (nu + 1) doubles (csrc/rmpc_exchange.cuh)."""
+    from robot_mpcs_b200.planner.solver import RmpcDims, load_library
+    lib = load_library(os.path.join(SOLVERS, "boxer_n3_01_H30_noSlack"))
+    dims = RmpcDims()
+    lib.rmpc_get_dims(ctypes.byref(dims))
+    f = lib.rmpc_exchange_region_bytes
+    for world, rows, depth in [(1, 1, 1), (2, 4096, 8), (8, 131072, 8), (16, 7, 3)]:
+        head = 32 + 8 * depth * world + 8 * world + 8 * depth
+        want = (head + 255) // 256 * 256 + 8 * depth * world * rows * (dims.nu + 1)
+        assert f(world, rows, depth) == want
+    assert f(0, 1, 1) == 0 and f(17, 1, 1) == 0 and f(2, 0, 1) == 0 and f(2, 1, 0) == 0
