@@ -650,7 +650,7 @@ def run_ours(args):
                         "note": "value needs several batches in flight (streams); roofline.one_batch_alone is what a closed loop, whose next step depends on this one, gets"},
                 "converged_fraction": rec["converged_fraction"], "mean_iters": rec["mean_iters"], "wall_s": rec["wall_s"], "gpu_launches": rec["gpu_launches"],
                 "roofline": rec["roofline"], "e2e": rec["e2e"], "clocks": rec["clocks"]}
-        for k in ("cpu_baseline", "single_solve_latency", "precision_1"):
+        for k in ("cpu_baseline", "single_solve_latency", "precision_1", "remeasured"):
             if k in rec:
                 line[k] = rec[k]
         if subs:
