@@ -18,7 +18,7 @@ init_process_group("nccl", device_id=dev)
 sdir = os.path.join(ROOT, "robot_mpcs_b200", "solvers", "boxer_n3_01_H30_noSlack")
 pm = yaml.safe_load(open(os.path.join(sdir, "paramMap.yaml")))
 from robot_mpcs_b200.parallel import shard_bounds
-steps, depth = 30, 4
+steps, depth = int(os.environ.get("XR_STEPS", "30")), int(os.environ.get("XR_DEPTH", "4"))
 total = 1024 * world - 7                              # the last shard is short
 per = -(-total // world)
 lo, hi = shard_bounds(total, rank, world)
