@@ -160,6 +160,8 @@ RMPC_HD void load_params(const PV& pv, int k, T* p) {
 
 // ------------------------------------------------------------------------------------------------
 // Shared (per problem) storage.  GPU: shared memory of the warp that owns the problem; host: heap.
+template <class M, class = void> struct AsksForSharedState { static constexpr bool value = false; };
+template <class M> struct AsksForSharedState<M, decltype(void(M::STATE_IN_SHARED))> { static constexpr bool value = M::STATE_IN_SHARED; };
 template <class M> struct Dims {
   // The Riccati algebra runs on the variables the Newton system couples (DynS::NXC states + NU inputs, "compact" indices)
   static constexpr int RX = DynS<M>::NXC, RV = RX + M::NU;
@@ -182,10 +184,12 @@ template <class M> struct Dims {
   // more in resident problems than it saves.  B200, r2n/r2o A/B (registers -> shared): panda 436 k -> 489 k solves/s and
   // B = 1 latency 1.27 -> 0.88 ms; pointRobot 3.33 M -> 3.58 M; boxer N = 30 743 k -> 758 k, latency 1.11 -> 0.90 ms;
   // boxer N = 40 424 k -> 399 k (kept in registers / local memory).  -DRMPC_STATE_SH=0/1 forces either form.
+  // A traits class can ask for the shared-memory form with `static constexpr bool STATE_IN_SHARED = true` (the single-launch
+  // kernel for batches of <= 32 problems does: occupancy is no concern there, and B = 1 of the N = 40 model runs 1.28 -> 0.99 ms).
 #if defined(RMPC_STATE_SH)
   static constexpr bool STATE_SH = RMPC_STATE_SH != 0;
 #else
-  static constexpr bool STATE_SH = M::N <= 32 || M::NH >= 24;
+  static constexpr bool STATE_SH = M::N <= 32 || M::NH >= 24 || AsksForSharedState<M>::value;
 #endif
   static constexpr int NLS = STATE_SH ? 2 * M::NH : 2;
   template <class T> static constexpr int nqs() {

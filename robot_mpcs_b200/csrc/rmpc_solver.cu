@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <atomic>
 #include <mutex>
+#include <type_traits>
 
 #include "model_traits.h"
 #ifndef RMPC_WARPS_FIXED
@@ -84,6 +85,7 @@ struct rmpc_solver {
   int blocks_per_sm, blocks_per_sm_sh, blocks_per_sm_all, sm_count;
   int bps_lowp, bps_resume;   // resident blocks per SM of the two kernels of a mixed-precision solve
   size_t smem_bytes;  // dynamic shared memory per block
+  size_t smem_bytes_all;   // ... of the single-launch kernel for small batches (state in shared memory for every model)
   // device staging for the host entry points: one packed input block and one packed output block
   double* d_in;         // xinit | x0 | params
   double* d_out;        // z | action | obj res_stat res_eq res_ineq res_comp | exitflag iters (ints)
@@ -104,6 +106,13 @@ struct rmpc_solver {
 using Shared = ProblemShared<M, double>;
 using I32 = Ipm<M, double, 32>;
 constexpr size_t kSharedPerWarp = (sizeof(Shared) + 15) / 16 * 16;
+// The single-launch kernel for batches of <= 32 problems (the latency path) keeps multipliers and slacks in shared memory for
+// every model: with at most 32 problems on 148 SMs occupancy does not matter, local-memory round trips do (r3s A/B, N = 40:
+// B = 1 p50 1.28 -> 0.99 ms, p99 4.98 -> 3.81 ms, while the same form costs a full batch 5 % of its throughput).
+struct LatencyTraits : ModelTraits { static constexpr bool STATE_IN_SHARED = true; };
+template <int MODE> using ModelOf = typename std::conditional<MODE == I32::kAll, LatencyTraits, M>::type;
+using SharedL = ProblemShared<LatencyTraits, double>;
+constexpr size_t kSharedLPerWarp = (sizeof(SharedL) + 15) / 16 * 16;
 // Warps (= problems) per thread block.  With more than one, the warps of a block meet at the top of every solver
 // iteration (Group<32>::align) so that they walk through the same code together and share instruction-cache fills.
 // Measured on B200 (boxer, 20 steps): 1 warp/block 702 k solves/s, 2: 622 k, 3: 574 k, 7: 534 k — waiting for the
@@ -125,7 +134,8 @@ struct SolveArgs {
   int control_mode;
 };
 
-__device__ __forceinline__ void write_outputs(const SolveArgs& a, const Shared& S, int lane, int b, const Info& inf) {
+template <class SharedT>
+__device__ __forceinline__ void write_outputs(const SolveArgs& a, const SharedT& S, int lane, int b, const Info& inf) {
   if (a.action && lane < M::NU) {
     // "acc": u of stage 1; "vel": z_2[nvar-2nu : nvar-nu]  (planner/mpcPlanner.py:275-281)
     a.action[(size_t)b * M::NU + lane] =
@@ -191,7 +201,10 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__
              int* __restrict__ head) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5;
-  Shared& S = *reinterpret_cast<Shared*>(smem_raw + warp * kSharedPerWarp);
+  using MM = ModelOf<MODE>;
+  using SharedM = ProblemShared<MM, double>;
+  using IpmM = Ipm<MM, double, 32>;
+  SharedM& S = *reinterpret_cast<SharedM*>(smem_raw + warp * ((sizeof(SharedM) + 15) / 16 * 16));
   Group<32> g{int(threadIdx.x & 31)};
   const int n = MODE == I32::kAll ? B : *count;
   for (;;) {
@@ -209,7 +222,7 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__
     const ParamView<double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
     Info inf;
     {
-      I32 ipm(g, S, pv, a.opt);
+      IpmM ipm(g, S, pv, a.opt);
       if constexpr (MODE == I32::kResume)
         ipm.solve_resume(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR, a.z_out ? a.z_out + (size_t)b * M::N * M::NVAR : nullptr,
                          a.ho.z + (size_t)b * M::N * M::NVAR, a.ho.lam + (size_t)b * M::N * M::NH, a.ho.mu[b], a.ho.it[b], inf);
@@ -404,13 +417,15 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   size_t smem = kSharedPerWarp * kWarps;
   if (const char* pad = getenv("RMPC_PAD_SMEM_KB")) smem += (size_t)atoi(pad) * 1024;  // experiment knob: fewer resident problems per SM
   s->smem_bytes = smem;
+  const size_t smem_all = kSharedLPerWarp * kWarps;
+  s->smem_bytes_all = smem_all;
   if ((e = cudaFuncSetAttribute(solve_kernel<I32::kFeasible>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(solve_kernel<I32::kShifted>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
-      (e = cudaFuncSetAttribute(solve_kernel<I32::kAll>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess)
+      (e = cudaFuncSetAttribute(solve_kernel<I32::kAll>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_all)) != cudaSuccess)
     return fail("cudaFuncSetAttribute(shared memory)", e);
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm, solve_kernel<I32::kFeasible>, 32 * kWarps, smem)) != cudaSuccess ||
       (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_sh, solve_kernel<I32::kShifted>, 32 * kWarps, smem)) != cudaSuccess ||
-      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_all, solve_kernel<I32::kAll>, 32 * kWarps, smem)) != cudaSuccess)
+      (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->blocks_per_sm_all, solve_kernel<I32::kAll>, 32 * kWarps, smem_all)) != cudaSuccess)
     return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor", e);
   if ((e = cudaFuncSetAttribute(solve_kernel<I32::kResume>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess ||
       (e = cudaFuncSetAttribute(lowp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSharedFPerWarp)) != cudaSuccess)
@@ -540,7 +555,7 @@ static int launch_solve(rmpc_solver* s, int B, const SolveArgs& a, cudaStream_t 
     CK(cudaMemsetAsync(sl.q, 0, 8 * sizeof(int), st));
     long grid = (long)s->blocks_per_sm_all * s->sm_count;
     if (grid > need) grid = need;
-    solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, st>>>(B, a, nullptr, nullptr, sl.q + 2);
+    solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes_all, st>>>(B, a, nullptr, nullptr, sl.q + 2);
     g_launches++;
     CK(cudaGetLastError());
     CK(cudaEventRecord(sl.ev_done, st));
@@ -660,7 +675,7 @@ static int latency_solve(rmpc_solver* s, int B, const double* xinit, const doubl
     if (e == cudaSuccess) {
       long grid = (long)s->blocks_per_sm_all * s->sm_count;
       if (grid > B) grid = B;
-      solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes, s->hstream>>>(B, a, nullptr, nullptr, s->lat_q + 2);
+      solve_kernel<I32::kAll><<<(unsigned)grid, 32 * kWarps, s->smem_bytes_all, s->hstream>>>(B, a, nullptr, nullptr, s->lat_q + 2);
       e = cudaGetLastError();
     }
     // outputs: from the first wanted section to the end of the flags (z is large and first, so it is skipped when unwanted)
