@@ -16,7 +16,7 @@
  * Plain pointers and sizes only; no torch types.  All functions return 0 on success, negative on API error
  * (message via rmpc_last_error()).  Per-problem solver status is reported only through info.exitflag[]
  * with the FORCESPRO sign convention the reference tests (mpcPlanner.py:263): 1 optimal, 0 iteration limit,
- * <0 failure (-5 factorisation, -6 NaN/Inf, -7 no progress / locally infeasible, -8 initial guess on the wrong side
+ * <0 failure (-5 factorisation, -6 NaN/Inf — in the iteration, or in xinit / x0 / params (then no iteration is run: iters 0) —, -7 no progress / locally infeasible, -8 initial guess on the wrong side
  * of a ConstraintAvoidance pole, -9 the converged point touches or leaves the -100 <= z <= 100 box of the reference's NLP
  * (models/mpcModel.py:23-28,98-104), which this solver checks but does not carry as rows: not a solution of that NLP;
  * -1 the problem was never written: an internal error).

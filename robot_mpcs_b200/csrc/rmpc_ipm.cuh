@@ -633,6 +633,7 @@ struct Ipm {
     T mu, rho_pen = T(1), err_ref = T(1e300);
     T lm = T(0);  // adaptive Levenberg-Marquardt damping: grows when the line search has to cut the step, decays on full steps
     int it, ncreep = 0, it_ref = 0, gn_hold = 0, gn_len = 1;
+    bool skipped = false;   // refused before the first iteration (bad or non-finite initial point)
     Red<T> so;
   };
 
@@ -678,7 +679,7 @@ struct Ipm {
     // initial point: z from the guess, x_1 = xinit
     load_guess(xinit, z_in);
     T mu = T(opt.mu0);
-    bool pole0 = false, shifted = false;
+    bool pole0 = false, shifted = false, finite0 = true;
     if constexpr (MODE != kFeasible) {  // lanes without a stage take part in the "any shift left?" votes: they must hold zeros, not what the last problem left
       RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl)
@@ -694,9 +695,11 @@ struct Ipm {
         StageVal<M, T> sv;
         stage_values<M, T>(S.st[k].z, p, sv);
         pole0 = pole0 || sv.pole;
+        finite0 = finite0 && tabs(sv.f) < T(1e30);   // false for NaN and Inf: a state, guess or parameter that is not a number
         RMPC_UNROLL
         for (int r = 0; r < NH; ++r) {
           const T hv = sv.h[r];
+          finite0 = finite0 && tabs(hv) < T(1e30);
           // a violated row starts with a slack as large as its violation: the fraction-to-boundary rule then leaves room
           // for steps that remove only part of the shift.  kFeasible: the classification found every row >= delta, and
           // the row is taken as it is (no shift storage in that build).
@@ -715,7 +718,8 @@ struct Ipm {
     Loop L;
     L.mu = mu; L.it = 0;
     L.so.f = L.so.res_stat = L.so.res_eq = L.so.comp_max = L.so.shift_max = T(0);
-    if (g.any(pole0)) { info.exitflag = -8; L.it = opt.max_iter + 1; }
+    if (g.any(pole0)) { info.exitflag = -8; L.it = opt.max_iter + 1; L.skipped = true; }
+    if (g.any(!finite0)) { info.exitflag = -6; L.it = opt.max_iter + 1; L.skipped = true; }   // NaN / Inf in the inputs: no iteration is run
     // Rows that start infeasible are rare (a warm start whose obstacles moved onto the plan), and their bookkeeping
     // costs registers and instructions in every unrolled row loop: the iteration exists twice, and the copy that
     // knows about shifts runs only until the last shift of the problem has reached zero.
@@ -801,7 +805,7 @@ struct Ipm {
         load_guess(xinit, z_in);
       }
       const T mu = resume ? T(hmu) : T(opt.mu0);
-      bool pole0 = false;
+      bool pole0 = false, finite0 = true;
       RMPC_UNROLL_SL
       for (int sl = 0; sl < SLOTS; ++sl) {
         const int k = g.lane + G * sl;
@@ -811,8 +815,10 @@ struct Ipm {
           StageVal<M, T> sv;
           stage_values<M, T>(S.st[k].z, p, sv);
           pole0 = pole0 || sv.pole;
+          finite0 = finite0 && tabs(sv.f) < T(1e30);
           RMPC_UNROLL
           for (int r = 0; r < NH; ++r) {
+            finite0 = finite0 && tabs(sv.h[r]) < T(1e30);
             if (resume) {
               const T lr = tmax(T(hlam[k * NH + r]), T(1e-30));
               // the slack is the row's own value; where float32 rounding of z has eaten a tiny slack, a tenth of the centred
@@ -830,7 +836,8 @@ struct Ipm {
       L = Loop();
       L.mu = mu; L.it = resume ? hit : 0;
       L.so.f = L.so.res_stat = L.so.res_eq = L.so.comp_max = L.so.shift_max = T(0);
-      if (g.any(pole0)) { info.exitflag = -8; L.it = opt.max_iter + 1; }
+      if (g.any(pole0)) { info.exitflag = -8; L.it = opt.max_iter + 1; L.skipped = !resume; }
+      if (g.any(!finite0)) { info.exitflag = -6; L.it = opt.max_iter + 1; L.skipped = !resume; }
       iterate<false>(L, info);
       if (info.exitflag >= 0) break;
     }
@@ -1106,7 +1113,7 @@ struct Ipm {
       for (int e = g.lane; e < N * NV; e += G) zmax = fmaxf(zmax, float(tabs(S.st[e / NV].z[e % NV])));
       if (g.max(zmax) > 100.0f - 1e-4f) info.exitflag = -9;
     }
-    info.iters = L.it > opt.max_iter ? opt.max_iter : L.it;
+    info.iters = L.skipped ? 0 : (L.it > opt.max_iter ? opt.max_iter : L.it);
     info.obj = double(L.so.f);
     info.res_stat = double(L.so.res_stat);
     info.res_eq = double(L.so.res_eq);

@@ -375,3 +375,33 @@ def test_closed_loop_in_vel_mode_follows_its_own_plan(built):
     assert float(vm[0]) <= 1.0 + 1e-6 and float(vm[1]) <= 1.0 + 1e-6
     d0 = torch.linalg.norm(_dev(s["xinit"])[:, :2] - goal[:, :2], dim=1)
     assert float((d0 - r["goal_distance"]).mean()) > 1.0 and int(r["failures"].sum()) <= 2
+
+
+@pytest.mark.parametrize("B", [8, 96])          # single-launch kernel (B <= 32) and classify + two kernels
+@pytest.mark.parametrize("precision", [0, 1])
+def test_nan_and_inf_inputs_are_refused_without_touching_their_neighbours(built, B, precision):
+    """A state, guess or parameter that is not a number (a sensor glitch): exitflag -6 before the first iteration, iters 0, and
+    every other problem of the batch is solved exactly as without the bad ones.  FORCESPRO answers such inputs with a negative
+    exitflag as well; the reference prints it and applies no action (mpcPlanner.py:263-264, boxer_example.py:194)."""
+    import torch
+    sdir = "boxer_n3_01_H30_noSlack"
+    pm = _pm(sdir)
+    s = sc.boxer_radial(pm, B, seed=33)
+    solver = _solver(sdir, B)
+    solver.set_options(precision=precision)
+    clean = solver.solve_batch(_dev(s["xinit"]), _dev(s["x0"]), _dev(s["params"]))
+    x, x0, P = s["xinit"].copy(), s["x0"].copy(), s["params"].copy()
+    x[1, 0] = np.nan
+    x0[2, 3, 1] = np.nan
+    P[3, :, pm["goal"][0]] = np.inf
+    P[4, 5, pm["wu"][0]] = np.nan
+    x[5, 1] = -np.inf
+    bad = np.zeros(B, bool)
+    bad[1:6] = True
+    r = solver.solve_batch(_dev(x), _dev(x0), _dev(P))
+    flag, it = r["exitflag"].cpu().numpy(), r["iters"].cpu().numpy()
+    assert (flag[bad] == -6).all() and (it[bad] == 0).all(), (flag[:8], it[:8])
+    good = torch.as_tensor(~bad, device="cuda:0")
+    assert torch.equal(r["exitflag"][good], clean["exitflag"][good]) and torch.equal(r["iters"][good], clean["iters"][good])
+    assert torch.equal(r["z"][good], clean["z"][good]) and torch.equal(r["action"][good], clean["action"][good])
+    assert (clean["exitflag"] == 1).float().mean() > 0.95
