@@ -124,6 +124,14 @@ int rmpc_shift_horizon(rmpc_solver* s, int B, const double* z, double* x0, void*
  * stage k; the input part of x0 is left as it is.  Device pointers. */
 int rmpc_set_x0(rmpc_solver* s, int B, const double* xinit, double* x0, void* stream);
 
+/* One step of the plant for a headless closed loop: x_next[b] = Phi(x[b], u[b]), the discrete model the solver was generated
+ * from (models/mpcModel.py:65-69,118-120 and diff_drive_mpc_model.py:24-41: ERK2 with 5 nodes, in closed form).  It stands where
+ * the reference's examples call env.step(action) of the pybullet simulation (examples/boxer_example.py:205; unavailable on this
+ * box).  x[B][nx], u[B][nu] (the input; for control_mode "vel" the caller converts the velocity action first), exitflag[B] may be
+ * NULL: a problem with exitflag < 0 is stepped with u = 0, as the reference applies no action after a failed solve
+ * (boxer_example.py:194).  x_next may alias x.  Device pointers, asynchronous on `stream`. */
+int rmpc_plant_step(rmpc_solver* s, int B, const double* x, const double* u, const int* exitflag, double* x_next, void* stream);
+
 /* Batched parameter scatter (the set* loops of mpcPlanner.py:120-210): for every problem b and every stage k,
  * params[b][k][idx[j]] = values[b][j] (stage_varying == 0, values is [B][n_idx]) or values[b][k][j]
  * (stage_varying == 1, values is [B][N][n_idx]).  idx is a HOST array of paramMap indices (it travels by value with

@@ -294,6 +294,25 @@ __global__ void guess_kernel(long total, const double* __restrict__ xinit, doubl
   x0[bk * M::NVAR + v] = xinit[(bk / M::N) * M::NX + v];
 }
 
+// x+ = Phi(x, u) of the model the solver was generated from (rmpc_model.cuh dyn_value), one thread per problem; a problem whose
+// solve failed (exitflag < 0) gets u = 0, as the reference's loops do not apply a failed solve (examples/boxer_example.py:194)
+__global__ void plant_kernel(int B, const double* __restrict__ x, const double* __restrict__ u, const int* __restrict__ exitflag,
+                             double* __restrict__ x_next) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double z[M::NVAR], xn[M::NX];
+#pragma unroll
+  for (int i = 0; i < M::NX; ++i) z[i] = x[(size_t)b * M::NX + i];
+  const bool apply = !exitflag || exitflag[b] >= 0;
+#pragma unroll
+  for (int i = 0; i < M::NU; ++i) z[M::NX + i] = apply ? u[(size_t)b * M::NU + i] : 0.0;
+#pragma unroll
+  for (int i = 0; i < M::NVAR - M::NX - M::NU; ++i) z[M::NX + M::NU + i] = 0.0;
+  dyn_value<M, double>(z, xn);
+#pragma unroll
+  for (int i = 0; i < M::NX; ++i) x_next[(size_t)b * M::NX + i] = xn[i];
+}
+
 struct IdxList { int n; int v[kMaxIdx]; };
 
 __global__ void scatter_kernel(int B, int n_all, int off, int stage_varying, const __grid_constant__ IdxList idx,
@@ -773,6 +792,16 @@ int rmpc_set_x0(rmpc_solver* s, int B, const double* xinit, double* x0, void* st
   GUARD(s);
   const long total = (long)B * M::N * M::NX;
   guess_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(total, xinit, x0);
+  g_launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int rmpc_plant_step(rmpc_solver* s, int B, const double* x, const double* u, const int* exitflag, double* x_next, void* stream) {
+  if (!s || !x || !u || !x_next || B <= 0) { snprintf(g_err, sizeof g_err, "bad argument"); return -1; }
+  std::lock_guard<std::mutex> lock(s->mu);
+  GUARD(s);
+  plant_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(B, x, u, exitflag, x_next);
   g_launches++;
   CK(cudaGetLastError());
   return 0;

@@ -41,7 +41,7 @@ class RmpcInfo(ctypes.Structure):
 
 EXPORTS = ["rmpc_model_name", "rmpc_get_dims", "rmpc_default_options", "rmpc_last_error", "rmpc_create", "rmpc_destroy",
            "rmpc_set_options", "rmpc_get_options", "rmpc_solve_batch", "rmpc_solve_batch_strided", "rmpc_solve_batch_host", "rmpc_solve_batch_host_async", "rmpc_wait", "rmpc_fsd_constraints", "rmpc_shift_horizon",
-           "rmpc_set_params", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_solve_batch_static", "rmpc_static_max_batch", "rmpc_launch_count",
+           "rmpc_set_params", "rmpc_plant_step", "rmpc_set_x0", "rmpc_predict_obstacles", "rmpc_solve_batch_static", "rmpc_static_max_batch", "rmpc_launch_count",
            "rmpc_exchange_region_bytes", "rmpc_ipc_alloc", "rmpc_ipc_open", "rmpc_ipc_close", "rmpc_ipc_free", "rmpc_exchange_create",
            "rmpc_exchange_destroy", "rmpc_exchange_publish", "rmpc_exchange_collect", "rmpc_exchange_join", "rmpc_exchange_status"]
 
@@ -80,6 +80,7 @@ def load_library(solver_dir: str, lib_dir: Optional[str] = None) -> ctypes.CDLL:
                                          ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_int,
                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_void_p]
     lib.rmpc_set_x0.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+    lib.rmpc_plant_step.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5
     lib.rmpc_predict_obstacles.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
     lib.rmpc_solve_batch_static.argtypes = ([ctypes.c_int] + [ctypes.c_void_p] * 5 + [ctypes.POINTER(RmpcInfo), ctypes.POINTER(RmpcOptions), ctypes.c_void_p])
@@ -264,6 +265,24 @@ class Solver:
         if self.lib.rmpc_set_x0(self._h, B, xinit.data_ptr(), x0.data_ptr(), ctypes.c_void_p(stream)) != 0:
             raise SolverError(self._err())
         return x0
+
+    def plant_step(self, x, u, exitflag=None, out=None):
+        """x+[B,nx] of the model the solver was generated from (the plant of a headless closed loop); problems with
+        exitflag < 0 are stepped with u = 0.  CUDA float64 tensors; `out` may be `x`."""
+        B = x.shape[0]
+        self._ensure(B)
+        x = x.to(torch.float64).contiguous()
+        u = u.to(torch.float64).contiguous()
+        if out is None:
+            out = torch.empty_like(x)
+        ef = None
+        if exitflag is not None:
+            ef = exitflag.to(torch.int32).contiguous()
+        stream = torch.cuda.current_stream(x.device).cuda_stream
+        if self.lib.rmpc_plant_step(self._h, B, x.data_ptr(), u.data_ptr(), ef.data_ptr() if ef is not None else None,
+                                    out.data_ptr(), ctypes.c_void_p(stream)) != 0:
+            raise SolverError(self._err())
+        return out
 
     def set_params(self, params, idx, values):
         """params[B,N,npar] (CUDA, float64) <- values[B,len(idx)] or values[B,N,len(idx)] at paramMap indices idx."""

@@ -130,15 +130,16 @@ def closed_loop(planner, x0: torch.Tensor, goal: torch.Tensor, steps: int, epsil
         info_iters = planner._last_iters if hasattr(planner, "_last_iters") else None
         if info_iters is not None:
             iters[t] = info_iters.to(torch.float64).mean()
-        ok = (flag >= 0)[:, None]
         if planner._config.control_mode == "vel":
             # the action is the velocity planned for stage 2 (mpcPlanner.py:275-278); the plant is driven by inputs, and for
             # these models v+ = v + dt u, so the input that realises it is (action - v) / dt — the plan's own u_1
             vel = x[:, 2 * n:2 * n + action.shape[1]] if diffdrive else x[:, n:2 * n]
             action = (action - vel) / dt
-        u = torch.where(ok, action, torch.zeros_like(action))   # boxer_example.py:194: a failed solve is not applied
         failures += (flag < 0).to(torch.int64)
-        x = plant_step(x, u, dt, diffdrive)
+        # the plant is the model the solver was generated from, stepped by the library's own kernel (one launch instead of the
+        # ~100 elementwise launches of `plant_step` above, which stays as the torch statement of the same model for the tests);
+        # boxer_example.py:194: a failed solve is not applied
+        x = planner._solver.plant_step(x, action, flag)
         z_prev = z
         d = torch.linalg.norm(x[:, :2] - goal[:, :2], dim=1)
         newly = (d <= epsilon) & ~reached

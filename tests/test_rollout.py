@@ -119,3 +119,28 @@ def test_bench_rollout_records(built, workload, T):
     assert r["mean_iters_warm"] < r["mean_iters_first_step"]          # warm starts pay
     if workload == "rollout_boxer_fsd":
         assert r["reached_fraction"] >= 0.95 and r["scenarios_reached_per_s"] > 0
+
+
+@pytest.mark.parametrize("sdir,diffdrive", [("pointRobot_n3_005_H20_noSlack", False), ("boxer_n3_01_H30_noSlack", True)])
+def test_plant_kernel_is_the_models_discrete_dynamics(built, sdir, diffdrive):
+    """rmpc_plant_step against the torch statement of the same model (rollout.plant_step: explicit midpoint, 5 substeps;
+    models/mpcModel.py:65-69,118-120, diff_drive_mpc_model.py:24-41); failed solves are stepped with u = 0; in place."""
+    import torch
+    from robot_mpcs_b200.planner.solver import Solver
+    from robot_mpcs_b200.rollout import plant_step
+    B = 257
+    solver = Solver.from_directory(os.path.join(SOLVERS, sdir), device=0, max_batch=B)
+    g = torch.Generator(device="cpu").manual_seed(3)
+    x = (torch.rand(B, solver.nx, generator=g, dtype=torch.float64) * 4 - 2).cuda()
+    if diffdrive:
+        x[:, 3:6] = 0.0
+    u = (torch.rand(B, solver.nu, generator=g, dtype=torch.float64) * 2 - 1).cuda()
+    flag = torch.ones(B, dtype=torch.int32, device="cuda:0")
+    flag[::5] = -7
+    want = plant_step(x, torch.where((flag >= 0)[:, None], u, torch.zeros_like(u)), solver.dt, diffdrive)
+    got = solver.plant_step(x, u, flag)
+    assert float((got - want).abs().max()) < 1e-12
+    assert torch.equal(solver.plant_step(x, u), solver.plant_step(x, u, torch.ones_like(flag)))
+    x2 = x.clone()
+    solver.plant_step(x2, u, flag, out=x2)
+    assert torch.equal(x2, got)
