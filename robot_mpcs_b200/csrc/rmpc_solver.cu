@@ -452,6 +452,13 @@ rmpc_solver* rmpc_create(int device, int max_batch) {
   if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->bps_resume, solve_kernel<I32::kResume>, 32 * kWarps, smem)) != cudaSuccess ||
       (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->bps_lowp, lowp_kernel, 32, kSharedFPerWarp)) != cudaSuccess)
     return fail("cudaOccupancyMaxActiveBlocksPerMultiprocessor(mixed precision)", e);
+  // L1 against resident problems (r3c, profiles/r3c_l1_carveout_experiment.txt): the driver's default carve-out already leaves panda
+  // 60 KB of L1 beside its four problems per SM; one problem fewer with 92 KB of L1 measures the same throughput (474 against 487 k)
+  // and a slower lone batch (3.1 against 2.5 ms), and the other models lose 0-3 %.  The two knobs below stay for experiments.
+  if (const char* pct = getenv("RMPC_CARVEOUT_PCT")) {  // experiment knob: shared-memory carve-out of the hot kernel in percent (the rest of the 256 KB is L1)
+    if ((e = cudaFuncSetAttribute(solve_kernel<I32::kFeasible>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(pct))) != cudaSuccess)
+      return fail("cudaFuncSetAttribute(carve-out)", e);
+  }
   if (const char* cap = getenv("RMPC_MAX_BLOCKS_PER_SM")) {  // experiment knob: fewer problems in flight per SM
     const int c = atoi(cap);
     if (c > 0 && c < s->blocks_per_sm) s->blocks_per_sm = c;
