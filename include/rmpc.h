@@ -87,7 +87,8 @@ int rmpc_get_options(const rmpc_solver* s, rmpc_options* out);
  * on `stream` (a cudaStream_t passed as void*, NULL = default stream).  z_out / action_out / info may be NULL; z_out may
  * alias x0 (every problem's guess is read by the one kernel that then writes its plan).
  * Launches: a 16-byte memset of the call's queue slot, classify_kernel (every problem is classified once: does a row of
- * its initial guess start infeasible? -> two index lists), then two persistent solve kernels side by side (one warp per
+ * its initial guess start infeasible? -> two index lists; and do all its stages carry the same parameter block? -> the solve then
+ * reads stage 1's block for every stage, one address per warp instead of N, with identical results), then two persistent solve kernels side by side (one warp per
  * problem, each pulling from its own list): feasible starts on `stream`, infeasible starts on a side stream forked from
  * and joined to it.  B <= 32 takes a single launch that classifies inside the solve. */
 int rmpc_solve_batch(rmpc_solver* s, int B, const double* xinit, const double* x0, const double* params,

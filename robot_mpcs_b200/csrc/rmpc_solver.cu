@@ -123,6 +123,11 @@ static_assert(kWarps >= 1, "one problem does not fit into the shared memory of a
 #ifndef RMPC_MIN_BLOCKS
 #define RMPC_MIN_BLOCKS 1   // resident blocks per SM the register allocation must allow
 #endif
+// Bit of a problem-list entry: every stage of the problem carries the same parameter block (true for every set* of the reference
+// except per-stage setLinearConstraints and updateDynamicObstacles, mpcPlanner.py:120-210).  The solve then reads stage 1's block
+// for all stages: the lanes of a warp load one address instead of N, one L1 line instead of N (what rmpc_solve_batch_strided with
+// stage stride 0 gives a caller who knows it: boxer +4 %), with bit-identical results.
+constexpr int kStageInvariant = 1 << 30;
 struct Handoff { const float *z, *lam, *mu; const int* it; };
 struct SolveArgs {
   Handoff ho;        // mixed precision only: state left by the float32 pass
@@ -162,7 +167,7 @@ __global__ void __launch_bounds__(256) classify_kernel(int B, const __grid_const
   const int warps = (gridDim.x * blockDim.x) >> 5;
   for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
     const ParamView<double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
-    bool shifted = false;
+    bool shifted = false, varies = false;
 #pragma unroll
     for (int sl = 0; sl < I32::SLOTS; ++sl) {
       const int k = lane + 32 * sl;
@@ -176,6 +181,9 @@ __global__ void __launch_bounds__(256) classify_kernel(int B, const __grid_const
           for (int i = 0; i < M::NX; ++i) z[i] = a.xinit[(size_t)b * M::NX + i];
         }
         load_params<M, double>(pv, k, p);
+        // do this stage's parameters differ from stage 1's?  (every lane reads the same address: one transaction per parameter)
+#pragma unroll
+        for (int j = 0; j < M::NPAR; ++j) varies = varies || !(p[j] == pv.get(0, j));
         StageVal<M, double> sv;
         stage_values<M, double>(z, p, sv);
 #pragma unroll
@@ -183,9 +191,10 @@ __global__ void __launch_bounds__(256) classify_kernel(int B, const __grid_const
       }
     }
     shifted = __any_sync(0xffffffffu, shifted) != 0;
+    varies = __any_sync(0xffffffffu, varies) != 0;
     if (lane == 0) {
       const int at = atomicAdd(q + (shifted ? 1 : 0), 1);
-      list[(shifted ? max_batch : 0) + at] = b;
+      list[(shifted ? max_batch : 0) + at] = b | (varies ? 0 : kStageInvariant);
     }
   }
 }
@@ -214,12 +223,14 @@ solve_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__
       if (MODE != I32::kAll) b = b < n ? list[b] : B;   // kFeasible, kShifted, kResume: the problems of a list
     }
     b = __shfl_sync(0xffffffffu, b, 0);
+    const bool invariant = MODE != I32::kAll && (b & kStageInvariant) != 0;
+    if (MODE != I32::kAll) b &= ~kStageInvariant;
     if (b >= B) {
       // out of work: keep meeting the other warps of the block at their iteration rendezvous until all are out of work
       if (kWarps > 1) while (!__syncthreads_and(1)) {}
       break;
     }
-    const ParamView<double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
+    const ParamView<double> pv{a.params + (size_t)b * a.p_bs, invariant ? 0 : a.p_ss, 1};
     Info inf;
     {
       IpmM ipm(g, S, pv, a.opt);
@@ -256,8 +267,10 @@ lowp_kernel(int B, const __grid_constant__ SolveArgs a, const int* __restrict__ 
     int b = 0;
     if (g.lane == 0) { b = atomicAdd(head, 1); b = b < n ? list[b] : B; }
     b = __shfl_sync(0xffffffffu, b, 0);
+    const bool invariant = (b & kStageInvariant) != 0;
+    b &= ~kStageInvariant;
     if (b >= B) break;
-    const ParamView<float, double> pv{a.params + (size_t)b * a.p_bs, a.p_ss, 1};
+    const ParamView<float, double> pv{a.params + (size_t)b * a.p_bs, invariant ? 0 : a.p_ss, 1};
     {
       IF ipm(g, S, pv, lo);
       ipm.solve_lowp(a.xinit + (size_t)b * M::NX, a.x0 + (size_t)b * M::N * M::NVAR, hz + (size_t)b * M::N * M::NVAR,
@@ -397,7 +410,7 @@ static void free_all(rmpc_solver* s) {
 }
 
 rmpc_solver* rmpc_create(int device, int max_batch) {
-  if (max_batch <= 0) { snprintf(g_err, sizeof g_err, "max_batch must be positive"); return nullptr; }
+  if (max_batch <= 0 || max_batch >= kStageInvariant) { snprintf(g_err, sizeof g_err, "max_batch must be in (0, 2^30)"); return nullptr; }
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || device < 0 || device >= ndev) {
