@@ -395,6 +395,9 @@ class Bench:
                     raise SystemExit(f"--params compressed: workload {workload} has stage-varying parameters")
                 devt["params"] = p3[:, 0].contiguous()
             sets.append(devt)
+        import gc
+        gc.collect()   # the previous workload's pinned host buffers are freed now, not inside the timed region (cudaFreeHost blocks the driver)
+        torch.cuda.synchronize(dev)
         tp = self.throughput(solver, sets, steps, warmup, nstreams, B)
         # ---- one batch alone (what a closed loop sees: the next step depends on this one): L2 flushed, events around the call
         k_ms = rr = None
