@@ -66,3 +66,27 @@ def test_twin_reaches_basin_agreement_floor(built, name):
         rel = np.abs(r["z"][b] - zo).max() / np.abs(zo).max()
         same += bool(rel < 1e-4 and abs(r["obj"][b] - c["obj"]) <= 1e-5 * abs(c["obj"]))
     assert same >= FLOORS[name] * valid, (name, same, valid)
+
+
+def test_twin_refuses_non_finite_inputs_before_the_first_iteration(built):
+    """The algorithm's host build (same template as the kernel): NaN / Inf in xinit, x0 or the parameters -> exit flag -6, no iteration,
+    neighbours unaffected (the GPU form of this test is tests/test_gpu_features.py::test_nan_and_inf_inputs_...)."""
+    import yaml
+    from oracle.build_twin import Twin
+    from robot_mpcs_b200 import scenarios as sc
+    for sdir, gen in [("boxer_n3_01_H30_noSlack", sc.boxer_radial), ("pointRobot_n3_005_H20_noSlack", sc.point_robot_sweep),
+                      ("panda_n7_005_H20_noSlack", sc.panda)]:
+        pm = yaml.safe_load(open(os.path.join(SOLVERS, sdir, "paramMap.yaml")))
+        s = gen(pm, 12)
+        tw = Twin(os.path.join(SOLVERS, sdir))
+        clean = tw.solve(s["xinit"], s["x0"], s["params"])
+        x, x0, P = s["xinit"].copy(), s["x0"].copy(), s["params"].copy()
+        x[1, 0] = np.nan
+        x0[2, 3, 1] = np.nan
+        P[3, :, pm["goal"][0]] = np.inf
+        P[4, 5, pm["wu"][0]] = np.nan
+        x[5, 1] = -np.inf
+        r = tw.solve(x, x0, P)
+        assert (r["exitflag"][1:6] == -6).all() and (r["iters"][1:6] == 0).all(), (sdir, r["exitflag"], r["iters"])
+        keep = np.r_[0, 6:12]
+        assert np.array_equal(r["exitflag"][keep], clean["exitflag"][keep]) and np.array_equal(r["z"][keep], clean["z"][keep])
